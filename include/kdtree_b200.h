@@ -1,0 +1,86 @@
+/* kdtree_b200.h — C ABI of libkdtree_b200.so (host core + sm_100a kernels).
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; kd_last_error()
+ *     gives the message of the last failure on the calling thread;
+ *   - points are row-major float32 [n][dim]; point index i has the reference's
+ *     ID i + 1 (+ id_offset in forest mode, kdtree_mpi.cpp:223);
+ *   - a tree is `perm` (int32[n], IN-ORDER layout, values = point indices):
+ *     the node of range [lo, lo+n) is perm[lo + n/2], left = [lo, lo+n/2),
+ *     right = [lo+n/2+1, lo+n)  (shape rule of kdtree_sequential.cpp:51-56);
+ *   - device entry points take raw device pointers and a cudaStream_t passed as
+ *     void*; they never allocate: scratch comes from the caller (sizes from the
+ *     *_workspace_bytes functions) and they do not synchronise the stream
+ *     unless stated.
+ */
+#ifndef KDTREE_B200_H_
+#define KDTREE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* kd_last_error(void);
+int kd_version(void);
+void kd_free(void* p); /* releases buffers returned by the kd_format_* functions */
+
+/* ---- problem generation (reference Utility.cpp:6-18, kdtree_mpi.cpp:19-41) ---- */
+/* rows [n_rows][dim] of mt19937(seed) -> uniform_real_distribution<float>(-100,100), bit-exact. */
+int kd_generate_uniform(int seed, int dim, int64_t n_rows, float* out);
+/* rows [first_row, first_row + n_rows) of the same stream (O(first_row) skip-ahead). */
+int kd_generate_uniform_rows(int seed, int dim, int64_t first_row, int64_t n_rows, float* out);
+/* seeded Gaussian blobs (not in the reference; BASELINE.json config 4). */
+int kd_generate_clustered(int seed, int dim, int64_t n_rows, int n_clusters, float sigma, float* out);
+
+/* ---- CPU build / query / node materialisation (kdtree_sequential.cpp:30-136) ---- */
+/* select-based build under the total order (coord[axis], index); threads <= 0 -> hardware count. */
+int kd_build_cpu(const float* points, int64_t n, int dim, int32_t* perm, int threads);
+/* the reference's formulation (sort first n-1, take n/2) with the same total order. */
+int kd_build_cpu_sortref(const float* points, int64_t n, int dim, int32_t* perm);
+/* reference DFS (near side first, strict <, far side iff da*da < best).  Outputs are optional (NULL). */
+int kd_nearest_cpu(const float* points, int64_t n, int dim, const int32_t* perm, const float* queries,
+                   int64_t nq, int32_t* out_index, float* out_dist2, float* out_dist, int64_t* out_visited);
+/* Node{point,left,right} (Node.hpp:35-45) as three int32[n] arrays indexed by in-order slot; -1 = null. */
+int kd_materialize_nodes_cpu(int64_t n, const int32_t* perm, int32_t* node_point, int32_t* left, int32_t* right);
+int64_t kd_root_slot(int64_t n);
+/* checks shape-independent invariants of a perm built with the reference rule; returns #violations in *bad. */
+int kd_check_tree_cpu(const float* points, int64_t n, int dim, const int32_t* perm, int64_t* bad);
+
+/* ---- text protocol (Utility.cpp:21-63,122-124; Node.cpp:16-28) ---- */
+int kd_format_float(float v, char* buf, int cap);
+int kd_format_result_line(int id, float distance, char* buf, int cap);
+int kd_format_point(const float* coords, int dim, int id, char** out, size_t* len);
+int kd_format_tree(const float* points, int64_t n, int dim, const int32_t* perm, int id_offset, char** out,
+                   size_t* len);
+int kd_format_head_and_leaves(const float* points, int64_t n, int dim, const int32_t* perm, int id_offset,
+                              char** out, size_t* len);
+
+/* ---- single-GPU build (new; semantics of kdtree_sequential.cpp:30-66) ---- */
+size_t kd_build_workspace_bytes(int64_t n, int dim);
+/* points: device float32 [n][dim]; perm: device int32[n]; tree_points (optional, may be NULL): device
+ * float32 [n][dim] receiving the coordinates in in-order slot order. */
+int kd_build_gpu(const float* points, int64_t n, int dim, int32_t* perm, float* tree_points, void* workspace,
+                 size_t workspace_bytes, void* stream);
+/* synchronises the stream and reports a device-side failure of the last build that used `workspace` */
+int kd_build_status(const void* workspace, int64_t n, int dim, void* stream);
+/* number of kernel launches issued by the last kd_build_gpu call on this thread */
+int64_t kd_last_launch_count(void);
+
+/* ---- single-GPU query (new; semantics of kdtree_sequential.cpp:75-136) ---- */
+/* tree_points: [n][dim] in slot order (from kd_build_gpu or kd_gather_rows_gpu). Outputs optional. */
+int kd_nearest_gpu(const float* tree_points, const int32_t* perm, int64_t n, int dim, const float* queries,
+                   int64_t nq, int32_t* out_index, float* out_dist2, float* out_dist, int32_t* out_visited,
+                   void* stream);
+int kd_gather_rows_gpu(const float* points, const int32_t* perm, int64_t n, int dim, float* out, void* stream);
+int kd_materialize_nodes_gpu(int64_t n, const int32_t* perm, int32_t* node_point, int32_t* left, int32_t* right,
+                             void* stream);
+/* per-axis min/max of a point set: out_min[dim], out_max[dim] (device). */
+int kd_bbox_gpu(const float* points, int64_t n, int dim, float* out_min, float* out_max, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KDTREE_B200_H_ */

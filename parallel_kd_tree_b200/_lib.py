@@ -1,0 +1,86 @@
+"""ctypes binding of libkdtree_b200.so (declarations: include/kdtree_b200.h)."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+from . import build as _build
+
+_lock = threading.Lock()
+_lib = None
+
+c_i32p = C.POINTER(C.c_int32)
+c_i64p = C.POINTER(C.c_int64)
+c_f32p = C.POINTER(C.c_float)
+
+
+class KdError(RuntimeError):
+    pass
+
+
+def _declare(lib):
+    vp, i64, i32, f32 = C.c_void_p, C.c_int64, C.c_int, C.c_float
+    sigs = {
+        "kd_last_error": (C.c_char_p, []),
+        "kd_version": (i32, []),
+        "kd_free": (None, [vp]),
+        "kd_generate_uniform": (i32, [i32, i32, i64, vp]),
+        "kd_generate_uniform_rows": (i32, [i32, i32, i64, i64, vp]),
+        "kd_generate_clustered": (i32, [i32, i32, i64, i32, f32, vp]),
+        "kd_build_cpu": (i32, [vp, i64, i32, vp, i32]),
+        "kd_build_cpu_sortref": (i32, [vp, i64, i32, vp]),
+        "kd_nearest_cpu": (i32, [vp, i64, i32, vp, vp, i64, vp, vp, vp, vp]),
+        "kd_materialize_nodes_cpu": (i32, [i64, vp, vp, vp, vp]),
+        "kd_root_slot": (i64, [i64]),
+        "kd_check_tree_cpu": (i32, [vp, i64, i32, vp, vp]),
+        "kd_format_float": (i32, [f32, C.c_char_p, i32]),
+        "kd_format_result_line": (i32, [i32, f32, C.c_char_p, i32]),
+        "kd_format_point": (i32, [vp, i32, i32, C.POINTER(vp), C.POINTER(C.c_size_t)]),
+        "kd_format_tree": (i32, [vp, i64, i32, vp, i32, C.POINTER(vp), C.POINTER(C.c_size_t)]),
+        "kd_format_head_and_leaves": (i32, [vp, i64, i32, vp, i32, C.POINTER(vp), C.POINTER(C.c_size_t)]),
+        "kd_build_workspace_bytes": (C.c_size_t, [i64, i32]),
+        "kd_build_gpu": (i32, [vp, i64, i32, vp, vp, vp, C.c_size_t, vp]),
+        "kd_last_launch_count": (i64, []),
+        "kd_nearest_gpu": (i32, [vp, vp, i64, i32, vp, i64, vp, vp, vp, vp, vp]),
+        "kd_gather_rows_gpu": (i32, [vp, vp, i64, i32, vp, vp]),
+        "kd_materialize_nodes_gpu": (i32, [i64, vp, vp, vp, vp, vp]),
+        "kd_bbox_gpu": (i32, [vp, i64, i32, vp, vp, vp]),
+    }
+    for name, (res, args) in sigs.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError:
+            continue
+        fn.restype = res
+        fn.argtypes = args
+
+
+def lib():
+    """Load (building it first if the sources changed) the native library."""
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                path = _build.LIB
+                if os.environ.get("KD_B200_NO_BUILD") != "1":
+                    path = _build.build_library()
+                elif not path.exists():
+                    raise KdError(f"{path} is missing and KD_B200_NO_BUILD=1 forbids building it")
+                handle = C.CDLL(str(path))
+                _declare(handle)
+                _lib = handle
+    return _lib
+
+
+def check(status: int, what: str = "") -> None:
+    if status != 0:
+        msg = lib().kd_last_error()
+        raise KdError(f"{what}: {msg.decode() if msg else 'error ' + str(status)}")
+
+
+def take_string(ptr: C.c_void_p, length: C.c_size_t) -> str:
+    try:
+        return C.string_at(ptr.value, length.value).decode()
+    finally:
+        lib().kd_free(ptr)

@@ -1,0 +1,602 @@
+// Single-GPU kd-tree build for sm_100a.
+//
+// What is built: exactly the tree of the reference's build_tree_rec
+// (kdtree_sequential.cpp:30-66) under the total order (coord[axis], index):
+// for a range of n points whose LAST slot is "pinned" (never sorted,
+// kdtree_sequential.cpp:46-48), the node is the rank-n/2 element of the other
+// n-1, the n/2 smaller ones form the left range with their maximum in the left
+// range's last slot (so it is pinned one level down), the larger ones plus the
+// old pinned element form the right range.  How it is built is new: a
+// level-synchronous select + partition, no sort, no recursion.
+//
+//   K1  k_init / k_gather_keys   SoA working columns (+ per-level key gather for dim > kMaxCarry)
+//   K2  k_hist + k_scan          segmented MSB radix select on the 64-bit composite (key, index)
+//   K3  k_partition + k_fixup    unstable three-way partition, node emission, left-max -> last slot
+//   K4  k_finish                 whole sub-tree of a <= kFinishT-point range inside shared memory
+//
+// Ranges are never stored: range s of level l is found by walking the shape
+// rule (left n/2, right n-n/2-1) along the bits of s.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdint>
+#include <cstdio>
+
+#include "../../include/kdtree_b200.h"
+#include "build_plan.h"
+#include "kd_common.h"
+#include "kd_error.h"
+
+namespace kd {
+
+__device__ __forceinline__ void seg_range(unsigned N, int level, unsigned s, unsigned& lo, unsigned& n) {
+    unsigned l = 0, cnt = N;
+    for (int b = level - 1; b >= 0; --b) {
+        unsigned m = cnt >> 1;
+        if ((s >> b) & 1u) { l += m + 1; cnt = cnt - m - 1; } else { cnt = m; }
+    }
+    lo = l;
+    n = cnt;
+}
+
+// ------------------------------------------------------------------------------------------
+// K1: working columns
+// ------------------------------------------------------------------------------------------
+__global__ void k_init(const float* __restrict__ pts, unsigned N, int dim, int ncol, Cols dst) {
+    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    dst.idx[i] = (int32_t)i;
+    for (int c = 0; c < ncol; ++c) dst.c[c][i] = pts[(size_t)i * dim + c];
+}
+
+__global__ void k_state_init(SegState* st, unsigned N, int level, unsigned nseg) {
+    unsigned s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= nseg) return;
+    unsigned lo, n;
+    seg_range(N, level, s, lo, n);
+    SegState S;
+    S.prefix = 0ull;
+    S.rank = n >> 1;  // node = rank n/2 among the n-1 unpinned elements
+    S.cnt = n - 1;
+    S.curL = 0;
+    S.curR = 0;
+    S.shift = 64;
+    S.done = 0;
+    st[s] = S;
+}
+
+__global__ void k_gather_keys(const float* __restrict__ pts, int dim, int axis, const int32_t* __restrict__ idx,
+                              float* __restrict__ keybuf, unsigned N, int level, int cps) {
+    unsigned s = blockIdx.x / cps, j = blockIdx.x % cps;
+    unsigned lo, n;
+    seg_range(N, level, s, lo, n);
+    unsigned chunk = (n + cps - 1) / cps;
+    unsigned b = lo + j * chunk, e = min(b + chunk, lo + n);
+    for (unsigned i = b + threadIdx.x; i < e; i += blockDim.x)
+        keybuf[i] = pts[(size_t)idx[i] * dim + axis];
+}
+
+// ------------------------------------------------------------------------------------------
+// K2: radix select.  Pass d histograms digit d of the composite over the candidates that
+// still match the prefix chosen by passes 0..d-1.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void warp_hist_add(unsigned* sh, unsigned digit, bool valid) {
+    // one shared atomic per distinct digit in the warp: constant cost under any key distribution
+    unsigned peers = __match_any_sync(0xffffffffu, valid ? digit : 0xffffffffu);
+    if (valid && (__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&sh[digit], __popc(peers));
+}
+
+template <int BLOCK>
+__global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys, const int32_t* __restrict__ idx,
+                                                const SegState* __restrict__ st, unsigned* __restrict__ ghist,
+                                                unsigned N, int level, int cps, int d) {
+    __shared__ unsigned sh[kDigitBins];
+    unsigned s = blockIdx.x / cps, j = blockIdx.x % cps;
+    SegState S = st[s];
+    if (S.done) return;
+    unsigned lo, n;
+    seg_range(N, level, s, lo, n);
+    unsigned free_n = n - 1;  // the pinned last slot never takes part (kdtree_sequential.cpp:46-48)
+    unsigned chunk = (free_n + cps - 1) / cps;
+    unsigned b = lo + j * chunk, e = min(b + chunk, lo + free_n);
+    if (b >= e) return;
+    for (int t = threadIdx.x; t < kDigitBins; t += BLOCK) sh[t] = 0;
+    __syncthreads();
+    const int dsh = digit_shift(d);
+    const unsigned mask = (1u << digit_bits(d)) - 1u;
+    unsigned iters = (e - b + BLOCK - 1) / BLOCK;
+    if (d < 3) {
+        const int ks = dsh - 32;
+        const int ps = d == 0 ? 0 : digit_shift(d - 1) - 32;
+        const unsigned want = d == 0 ? 0u : (unsigned)(S.prefix >> digit_shift(d - 1));
+        for (unsigned it = 0; it < iters; ++it) {
+            unsigned i = b + it * BLOCK + threadIdx.x;
+            bool valid = i < e;
+            unsigned key = valid ? ordered_key(keys[i]) : 0u;
+            if (d > 0) valid = valid && ((key >> ps) == want);
+            warp_hist_add(sh, (key >> ks) & mask, valid);
+        }
+    } else {
+        const unsigned wantkey = (unsigned)(S.prefix >> 32);
+        const int ps = d == 3 ? 0 : digit_shift(d - 1);
+        const unsigned wantidx = d == 3 ? 0u : ((unsigned)(S.prefix & 0xffffffffull) >> ps);
+        for (unsigned it = 0; it < iters; ++it) {
+            unsigned i = b + it * BLOCK + threadIdx.x;
+            bool valid = i < e;
+            unsigned key = valid ? ordered_key(keys[i]) : 0u;
+            valid = valid && key == wantkey;
+            unsigned id = valid ? (unsigned)idx[i] : 0u;
+            if (d > 3) valid = valid && ((id >> ps) == wantidx);
+            warp_hist_add(sh, (id >> dsh) & mask, valid);
+        }
+    }
+    __syncthreads();
+    unsigned* gh = ghist + (size_t)s * kDigitBins;
+    for (int t = threadIdx.x; t < kDigitBins; t += BLOCK) {
+        unsigned v = sh[t];
+        if (v) atomicAdd(&gh[t], v);
+    }
+}
+
+// one CTA of 256 threads per range: locate the bin holding the wanted rank, extend the prefix, clear bins
+__global__ void __launch_bounds__(256) k_scan(SegState* st, unsigned* ghist, int d, int* err) {
+    __shared__ unsigned wsum[8];
+    __shared__ int fbin;
+    __shared__ unsigned fcum, fcnt;
+    unsigned s = blockIdx.x;
+    SegState S = st[s];
+    if (S.done) return;
+    unsigned* h = ghist + (size_t)s * kDigitBins;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (tid == 0) fbin = -1;
+    unsigned v[8], sum = 0;
+    uint4 a = reinterpret_cast<uint4*>(h)[tid * 2], bq = reinterpret_cast<uint4*>(h)[tid * 2 + 1];
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = bq.x; v[5] = bq.y; v[6] = bq.z; v[7] = bq.w;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) sum += v[k];
+    unsigned inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) wsum[w] = inc;
+    __syncthreads();
+    unsigned base = 0;
+    for (int k = 0; k < w; ++k) base += wsum[k];
+    unsigned c = base + inc - sum;
+    const unsigned r = S.rank;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        if (r >= c && r < c + v[k]) { fbin = tid * 8 + k; fcum = c; fcnt = v[k]; }
+        c += v[k];
+    }
+    reinterpret_cast<uint4*>(h)[tid * 2] = make_uint4(0, 0, 0, 0);
+    reinterpret_cast<uint4*>(h)[tid * 2 + 1] = make_uint4(0, 0, 0, 0);
+    __syncthreads();
+    if (tid == 0) {
+        if (fbin < 0) {
+            atomicExch(err, 1 + d);  // the histogram does not contain the wanted rank: internal error
+            S.done = 1;
+        } else {
+            S.prefix |= (unsigned long long)(unsigned)fbin << digit_shift(d);
+            S.rank = r - fcum;
+            S.cnt = fcnt;
+            S.shift = digit_shift(d);
+            S.done = (fcnt == 1u || d == kNumDigits - 1) ? 1 : 0;
+        }
+        st[s] = S;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K3: partition around the selected element.  Order inside the left / right parts is free
+// (the next level selects under a total order), so output slots are claimed with atomics.
+// ------------------------------------------------------------------------------------------
+struct MaxRec { unsigned long long comp; unsigned pos; unsigned valid; };
+
+template <int BLOCK, int IPT>
+__global__ void __launch_bounds__(BLOCK) k_partition(Cols src, Cols dst, int ncol, const float* __restrict__ keys,
+                                                     SegState* st, MaxRec* rec, int32_t* __restrict__ perm,
+                                                     float* __restrict__ tree_pts, int dim, unsigned N, int level,
+                                                     int cps) {
+    __shared__ unsigned s_cnt[2], s_base[2];
+    __shared__ unsigned long long s_wcomp[BLOCK / 32];
+    __shared__ unsigned s_wpos[BLOCK / 32];
+    const unsigned s = blockIdx.x / cps, j = blockIdx.x % cps;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const unsigned long long prefix = st[s].prefix;
+    const int shift = st[s].shift;
+    unsigned lo, n;
+    seg_range(N, level, s, lo, n);
+    const unsigned m = n >> 1, free_n = n - 1;
+    const unsigned chunk = (free_n + cps - 1) / cps;
+    const unsigned b = lo + j * chunk, e = min(b + chunk, lo + free_n);
+    const unsigned long long want = prefix >> shift;
+    unsigned long long best = 0ull;
+    unsigned bestpos = 0, bestvalid = 0;
+
+    if (j == (unsigned)cps - 1 && tid == 0) {  // the pinned element keeps its slot: last of the right range
+        unsigned p = lo + n - 1;
+        for (int c = 0; c < ncol; ++c) dst.c[c][p] = src.c[c][p];
+        dst.idx[p] = src.idx[p];
+    }
+    for (unsigned tb = b; tb < e; tb += BLOCK * IPT) {
+        if (tid < 2) s_cnt[tid] = 0;
+        __syncthreads();
+        unsigned key[IPT], rk[IPT];
+        int id[IPT];
+        signed char side[IPT];  // -1 left, 0 node, 1 right, 2 nothing
+#pragma unroll
+        for (int k = 0; k < IPT; ++k) {
+            unsigned i = tb + k * BLOCK + tid;
+            bool valid = i < e;
+            key[k] = valid ? ordered_key(keys[i]) : 0u;
+            id[k] = valid ? src.idx[i] : 0;
+            side[k] = 2;
+            if (valid) {
+                unsigned long long c = composite(key[k], (unsigned)id[k]) >> shift;
+                side[k] = c < want ? -1 : (c > want ? 1 : 0);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < IPT; ++k) {
+            unsigned bl = __ballot_sync(0xffffffffu, side[k] == -1);
+            unsigned br = __ballot_sync(0xffffffffu, side[k] == 1);
+            unsigned wl = 0, wr = 0;
+            if (lane == 0) {
+                if (bl) wl = atomicAdd(&s_cnt[0], __popc(bl));
+                if (br) wr = atomicAdd(&s_cnt[1], __popc(br));
+            }
+            wl = __shfl_sync(0xffffffffu, wl, 0);
+            wr = __shfl_sync(0xffffffffu, wr, 0);
+            unsigned lt = (1u << lane) - 1u;
+            rk[k] = side[k] == -1 ? wl + __popc(bl & lt) : wr + __popc(br & lt);
+        }
+        __syncthreads();
+        if (tid < 2) {
+            unsigned c = s_cnt[tid];
+            s_base[tid] = c ? atomicAdd(tid == 0 ? &st[s].curL : &st[s].curR, c) : 0u;
+        }
+        __syncthreads();
+        const unsigned baseL = lo + s_base[0], baseR = lo + m + 1 + s_base[1];
+#pragma unroll
+        for (int k = 0; k < IPT; ++k) {
+            unsigned i = tb + k * BLOCK + tid;
+            if (side[k] == 2) continue;
+            if (side[k] == 0) {
+                // the node of this range: final slot lo + n/2 (kdtree_sequential.cpp:51,65)
+                perm[lo + m] = id[k];
+                if (tree_pts && ncol)
+                    for (int c = 0; c < ncol; ++c) tree_pts[(size_t)(lo + m) * dim + c] = src.c[c][i];
+                continue;
+            }
+            unsigned p = (side[k] == -1 ? baseL : baseR) + rk[k];
+            for (int c = 0; c < ncol; ++c) dst.c[c][p] = src.c[c][i];
+            dst.idx[p] = id[k];
+            if (side[k] == -1) {
+                unsigned long long c = composite(key[k], (unsigned)id[k]);
+                if (!bestvalid || c > best) { best = c; bestpos = p; bestvalid = 1; }
+            }
+        }
+    }
+    // block-wide arg-max of the left-going composites -> one record per CTA
+    for (int o = 16; o > 0; o >>= 1) {
+        unsigned long long oc = __shfl_xor_sync(0xffffffffu, best, o);
+        unsigned op = __shfl_xor_sync(0xffffffffu, bestpos, o);
+        unsigned ov = __shfl_xor_sync(0xffffffffu, bestvalid, o);
+        if (ov && (!bestvalid || oc > best)) { best = oc; bestpos = op; bestvalid = 1; }
+    }
+    if (lane == 0) { s_wcomp[tid >> 5] = bestvalid ? best : 0ull; s_wpos[tid >> 5] = bestvalid ? bestpos : 0xffffffffu; }
+    __syncthreads();
+    if (tid == 0) {
+        MaxRec r{0ull, 0u, 0u};
+        for (int w = 0; w < BLOCK / 32; ++w)
+            if (s_wpos[w] != 0xffffffffu && (!r.valid || s_wcomp[w] > r.comp)) { r.comp = s_wcomp[w]; r.pos = s_wpos[w]; r.valid = 1; }
+        rec[blockIdx.x] = r;
+    }
+}
+
+// one warp per range: the largest left element goes to the left range's last slot (pinned next level)
+__global__ void __launch_bounds__(256) k_fixup(Cols dst, int ncol, const MaxRec* __restrict__ rec, unsigned N,
+                                               int level, unsigned nseg, int cps) {
+    unsigned s = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (s >= nseg) return;
+    const int lane = threadIdx.x & 31;
+    unsigned long long best = 0ull;
+    unsigned bestpos = 0, bestvalid = 0;
+    for (int t = lane; t < cps; t += 32) {
+        MaxRec r = rec[(size_t)s * cps + t];
+        if (r.valid && (!bestvalid || r.comp > best)) { best = r.comp; bestpos = r.pos; bestvalid = 1; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        unsigned long long oc = __shfl_xor_sync(0xffffffffu, best, o);
+        unsigned op = __shfl_xor_sync(0xffffffffu, bestpos, o);
+        unsigned ov = __shfl_xor_sync(0xffffffffu, bestvalid, o);
+        if (ov && (!bestvalid || oc > best)) { best = oc; bestpos = op; bestvalid = 1; }
+    }
+    if (!bestvalid) return;
+    unsigned lo, n;
+    seg_range(N, level, s, lo, n);
+    unsigned last = lo + (n >> 1) - 1;
+    if (bestpos == last) return;
+    if (lane < ncol) {
+        float a = dst.c[lane][bestpos], b = dst.c[lane][last];
+        dst.c[lane][bestpos] = b;
+        dst.c[lane][last] = a;
+    } else if (lane == ncol) {
+        int32_t a = dst.idx[bestpos], b = dst.idx[last];
+        dst.idx[bestpos] = b;
+        dst.idx[last] = a;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K4: finisher.  One CTA owns a range of n <= kFinishT points and builds its whole sub-tree
+// in shared memory: per sub-level a segmented bitonic sort of every sub-range's first n-1
+// positions (the reference's formulation, kdtree_sequential.cpp:46-56), points stay put and
+// a (key, slot) pair moves.  All slots are final at the end and are written out once.
+// ------------------------------------------------------------------------------------------
+constexpr int kFinishBlock = 512;
+
+__global__ void __launch_bounds__(kFinishBlock) k_finish(Cols src, int ncol, const float* __restrict__ pts, int dim,
+                                                         unsigned N, int level, int32_t* __restrict__ perm,
+                                                         float* __restrict__ tree_pts) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    constexpr int T = kFinishT;
+    unsigned lo, n;
+    seg_range(N, level, blockIdx.x, lo, n);
+    if (n == 0) return;
+    float* scol = reinterpret_cast<float*>(smem);                      // [ncol][T]  coordinates by slot
+    int32_t* sidx = reinterpret_cast<int32_t*>(scol + (size_t)ncol * T);  // [T]     point index by slot
+    unsigned* skey = reinterpret_cast<unsigned*>(sidx + T);            // [T]        sort key by position
+    unsigned* stab = skey + T;                                         // [T]        sub-range table (lo << 16 | n)
+    unsigned short* sord = reinterpret_cast<unsigned short*>(stab + T);  // [T]      slot by position
+    const int tid = threadIdx.x;
+    for (unsigned p = tid; p < n; p += kFinishBlock) {
+        sidx[p] = src.idx[lo + p];
+        for (int c = 0; c < ncol; ++c) scol[c * T + p] = src.c[c][lo + p];
+        sord[p] = (unsigned short)p;
+    }
+    if (tid == 0) stab[0] = n;  // sub-range 0 of sub-level 0: lo = 0, size n
+    __syncthreads();
+    for (int j = 0; (n >> j) >= 3u; ++j) {
+        const unsigned nsub = 1u << j;
+        const int axis = (level + j) % dim;
+        for (unsigned p = tid; p < n; p += kFinishBlock) {
+            unsigned slot = sord[p];
+            float f = ncol ? scol[axis * T + slot] : pts[(size_t)sidx[slot] * dim + axis];
+            skey[p] = ordered_key(f);
+        }
+        __syncthreads();
+        unsigned maxsort = (n >> j) - 1u;  // the left-most sub-range is the largest
+        unsigned P = 2;
+        int logHalf = 0;
+        while (P < maxsort) { P <<= 1; ++logHalf; }
+        const unsigned halfP = P >> 1, total = nsub << logHalf;
+        for (unsigned k = 2; k <= P; k <<= 1) {
+            int ljj = 31 - __clz(k >> 1);
+            for (unsigned jj = k >> 1; jj >= 1; jj >>= 1, --ljj) {
+                const bool flip = jj == (k >> 1);
+                for (unsigned t = tid; t < total; t += kFinishBlock) {
+                    unsigned sub = t >> logHalf, w = t & (halfP - 1u);
+                    unsigned tb = stab[sub];
+                    unsigned sn = tb & 0xffffu, slo = tb >> 16;
+                    if (sn < 3u) continue;
+                    unsigned sz = sn - 1u;
+                    unsigned i, l;
+                    const unsigned g = w >> ljj, r = w & (jj - 1u);
+                    if (flip) {
+                        i = g * k + r;
+                        l = g * k + (k - 1u - r);
+                    } else {
+                        i = g * 2u * jj + r;
+                        l = i + jj;
+                    }
+                    if (l >= sz) continue;
+                    unsigned a = slo + i, bb = slo + l;
+                    unsigned ka = skey[a], kb = skey[bb];
+                    bool sw = ka > kb;
+                    if (ka == kb) sw = sidx[sord[a]] > sidx[sord[bb]];
+                    if (sw) {
+                        skey[a] = kb;
+                        skey[bb] = ka;
+                        unsigned short oa = sord[a];
+                        sord[a] = sord[bb];
+                        sord[bb] = oa;
+                    }
+                }
+                __syncthreads();
+            }
+        }
+        // next sub-level's table: range s -> 2s (left n/2) and 2s+1 (right n-n/2-1), node slot drops out
+        unsigned ent[(T / 4 + kFinishBlock - 1) / kFinishBlock + 1];
+        int cnt = 0;
+        for (unsigned sidx2 = tid; sidx2 < nsub; sidx2 += kFinishBlock) ent[cnt++] = stab[sidx2];
+        __syncthreads();
+        cnt = 0;
+        for (unsigned sidx2 = tid; sidx2 < nsub; sidx2 += kFinishBlock) {
+            unsigned tb = ent[cnt++];
+            unsigned sn = tb & 0xffffu, slo = tb >> 16, m = sn >> 1;
+            stab[2 * sidx2] = (slo << 16) | m;
+            stab[2 * sidx2 + 1] = sn ? (((slo + m + 1u) << 16) | (sn - m - 1u)) : (slo << 16);
+        }
+        __syncthreads();
+    }
+    for (unsigned p = tid; p < n; p += kFinishBlock) {
+        unsigned slot = sord[p];
+        perm[lo + p] = sidx[slot];
+        if (tree_pts && ncol)
+            for (int c = 0; c < ncol; ++c) tree_pts[(size_t)(lo + p) * dim + c] = scol[c * T + slot];
+    }
+}
+
+__global__ void k_gather_rows(const float* __restrict__ pts, const int32_t* __restrict__ perm, unsigned N, int dim,
+                              float* __restrict__ out) {
+    size_t total = (size_t)N * dim;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        size_t row = e / dim;
+        int c = (int)(e - row * dim);
+        out[e] = pts[(size_t)perm[row] * dim + c];
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+static thread_local int64_t g_launches = 0;
+
+BuildPlan make_plan(int64_t n, int dim) {
+    BuildPlan p{};
+    p.n = n;
+    p.dim = dim;
+    p.ncol = dim <= kMaxCarry ? dim : 0;
+    // level at which every range fits the finisher (the left-most range is the largest: n >> level)
+    int lv = 0;
+    while ((n >> lv) > kFinishT) ++lv;
+    p.finish_level = lv;
+    p.max_seg = lv == 0 ? 1 : (1ll << (lv - 1));  // ranges of the deepest select/partition level
+    p.max_rec = p.max_seg + kTargetCtas;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    for (int b = 0; b < 2; ++b) {
+        for (int c = 0; c < p.ncol; ++c) p.off_col[b][c] = take((size_t)n * 4);
+        p.off_idx[b] = take((size_t)n * 4);
+    }
+    p.off_key = p.ncol ? 0 : take((size_t)n * 4);
+    p.off_state = take((size_t)p.max_seg * sizeof(SegState));
+    p.off_hist = take((size_t)p.max_seg * kDigitBins * 4);
+    p.off_rec = take((size_t)p.max_rec * 16);
+    p.off_err = take(256);
+    p.bytes = off;
+    return p;
+}
+
+static inline int ctas_per_seg(int64_t nseg, int64_t seg_n, int64_t min_chunk) {
+    int64_t want = (kTargetCtas + nseg - 1) / nseg;
+    int64_t cap = std::max<int64_t>(1, (seg_n + min_chunk - 1) / min_chunk);
+    return (int)std::max<int64_t>(1, std::min(want, cap));
+}
+
+#define KD_LAUNCH_CHECK(what)                                                              \
+    do {                                                                                   \
+        ++g_launches;                                                                      \
+        cudaError_t e_ = cudaGetLastError();                                               \
+        if (e_ != cudaSuccess) return fail(std::string(what) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+int build_gpu(const float* points, int64_t n, int dim, int32_t* perm, float* tree_points, void* workspace,
+              size_t workspace_bytes, cudaStream_t stream) {
+    if (!points || !perm || !workspace || n <= 0 || dim <= 0) return fail("kd_build_gpu: bad arguments");
+    if (n >= (1ll << 31)) return fail("kd_build_gpu: n must be below 2^31");
+    BuildPlan p = make_plan(n, dim);
+    if (workspace_bytes < p.bytes) return fail("kd_build_gpu: workspace too small");
+    g_launches = 0;
+    const size_t fin_smem = finish_smem_bytes(p.ncol);
+    {
+        cudaError_t e = cudaFuncSetAttribute(k_finish, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)finish_smem_bytes(kMaxCarry));
+        if (e != cudaSuccess) return fail(std::string("kd_build_gpu: cudaFuncSetAttribute: ") + cudaGetErrorString(e));
+    }
+    unsigned char* ws = (unsigned char*)workspace;
+    Cols buf[2];
+    for (int b = 0; b < 2; ++b) {
+        for (int c = 0; c < kMaxCarry; ++c) buf[b].c[c] = c < p.ncol ? (float*)(ws + p.off_col[b][c]) : nullptr;
+        buf[b].idx = (int32_t*)(ws + p.off_idx[b]);
+    }
+    float* keybuf = p.ncol ? nullptr : (float*)(ws + p.off_key);
+    SegState* st = (SegState*)(ws + p.off_state);
+    unsigned* ghist = (unsigned*)(ws + p.off_hist);
+    MaxRec* rec = (MaxRec*)(ws + p.off_rec);
+    int* err = (int*)(ws + p.off_err);
+    const unsigned N = (unsigned)n;
+
+    if (cudaMemsetAsync(ghist, 0, (size_t)p.max_seg * kDigitBins * 4, stream) != cudaSuccess ||
+        cudaMemsetAsync(err, 0, 256, stream) != cudaSuccess)
+        return fail("kd_build_gpu: cudaMemsetAsync failed");
+    k_init<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(points, N, dim, p.ncol, buf[0]);
+    KD_LAUNCH_CHECK("k_init");
+
+    int cur = 0;
+    for (int level = 0;; ++level) {
+        const int64_t nseg = 1ll << level;
+        if (level == p.finish_level) {
+            k_finish<<<(unsigned)nseg, kFinishBlock, fin_smem, stream>>>(buf[cur], p.ncol, points, dim, N, level, perm,
+                                                                        tree_points);
+            KD_LAUNCH_CHECK("k_finish");
+            break;
+        }
+        const int64_t seg_n = n >> level;
+        const int axis = level % dim;
+        const int cps_h = ctas_per_seg(nseg, seg_n, 8192);
+        const int cps_p = ctas_per_seg(nseg, seg_n, 2048);
+        k_state_init<<<(unsigned)((nseg + 255) / 256), 256, 0, stream>>>(st, N, level, (unsigned)nseg);
+        KD_LAUNCH_CHECK("k_state_init");
+        const float* keys;
+        if (p.ncol) {
+            keys = buf[cur].c[axis];
+        } else {
+            k_gather_keys<<<(unsigned)(nseg * cps_p), 256, 0, stream>>>(points, dim, axis, buf[cur].idx, keybuf, N,
+                                                                        level, cps_p);
+            KD_LAUNCH_CHECK("k_gather_keys");
+            keys = keybuf;
+        }
+        for (int d = 0; d < kNumDigits; ++d) {
+            k_hist<512><<<(unsigned)(nseg * cps_h), 512, 0, stream>>>(keys, buf[cur].idx, st, ghist, N, level, cps_h, d);
+            KD_LAUNCH_CHECK("k_hist");
+            k_scan<<<(unsigned)nseg, 256, 0, stream>>>(st, ghist, d, err);
+            KD_LAUNCH_CHECK("k_scan");
+        }
+        k_partition<256, 8><<<(unsigned)(nseg * cps_p), 256, 0, stream>>>(buf[cur], buf[cur ^ 1], p.ncol, keys, st, rec,
+                                                                        perm, tree_points, dim, N, level, cps_p);
+        KD_LAUNCH_CHECK("k_partition");
+        k_fixup<<<(unsigned)((nseg + 7) / 8), 256, 0, stream>>>(buf[cur ^ 1], p.ncol, rec, N, level, (unsigned)nseg,
+                                                               cps_p);
+        KD_LAUNCH_CHECK("k_fixup");
+        cur ^= 1;
+    }
+    if (tree_points && !p.ncol) {
+        k_gather_rows<<<148 * 8, 256, 0, stream>>>(points, perm, N, dim, tree_points);
+        KD_LAUNCH_CHECK("k_gather_rows");
+    }
+    return 0;
+}
+
+int64_t last_launches() { return g_launches; }
+
+}  // namespace kd
+
+extern "C" {
+
+size_t kd_build_workspace_bytes(int64_t n, int dim) {
+    if (n <= 0 || dim <= 0) return 0;
+    return kd::make_plan(n, dim).bytes;
+}
+
+int kd_build_gpu(const float* points, int64_t n, int dim, int32_t* perm, float* tree_points, void* workspace,
+                 size_t workspace_bytes, void* stream) {
+    return kd::build_gpu(points, n, dim, perm, tree_points, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int64_t kd_last_launch_count(void) { return kd::last_launches(); }
+
+int kd_build_status(const void* workspace, int64_t n, int dim, void* stream) {
+    if (!workspace || n <= 0 || dim <= 0) return kd::fail("kd_build_status: bad arguments");
+    kd::BuildPlan p = kd::make_plan(n, dim);
+    int err = 0;
+    cudaError_t e = cudaMemcpyAsync(&err, (const unsigned char*)workspace + p.off_err, sizeof(int),
+                                    cudaMemcpyDeviceToHost, (cudaStream_t)stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize((cudaStream_t)stream);
+    if (e != cudaSuccess) return kd::fail(std::string("kd_build_status: ") + cudaGetErrorString(e));
+    if (err) return kd::fail("kd_build_gpu: select lost its rank in digit pass " + std::to_string(err - 1));
+    return 0;
+}
+
+int kd_gather_rows_gpu(const float* points, const int32_t* perm, int64_t n, int dim, float* out, void* stream) {
+    if (!points || !perm || !out || n <= 0 || dim <= 0) return kd::fail("kd_gather_rows_gpu: bad arguments");
+    kd::k_gather_rows<<<148 * 8, 256, 0, (cudaStream_t)stream>>>(points, perm, (unsigned)n, dim, out);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : kd::fail(std::string("kd_gather_rows_gpu: ") + cudaGetErrorString(e));
+}
+
+}  // extern "C"

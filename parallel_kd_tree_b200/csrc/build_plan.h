@@ -1,0 +1,40 @@
+// Workspace layout and small PODs shared by the build kernels and their host drivers.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+
+namespace kd {
+
+constexpr int kMaxCarry = 4;      // dim <= kMaxCarry: coordinates travel with the points (SoA columns);
+                                  // larger dim: only indices move and keys are gathered per level
+constexpr int kFinishT = 4096;    // ranges of at most this many points are finished in shared memory
+constexpr int kTargetCtas = 148 * 16;
+
+struct SegState {
+    unsigned long long prefix;  // composite bits resolved so far (bits below `shift` are zero)
+    unsigned int rank;          // 0-based rank still wanted among the candidates
+    unsigned int cnt;           // candidates matching the prefix
+    unsigned int curL, curR;    // output cursors of the partition
+    int shift;                  // compare (composite >> shift) with (prefix >> shift)
+    int done;
+};
+
+struct Cols {
+    float* c[kMaxCarry];
+    int32_t* idx;
+};
+
+struct BuildPlan {
+    int64_t n;
+    int dim, ncol, finish_level;
+    int64_t max_seg, max_rec;
+    size_t off_col[2][kMaxCarry], off_idx[2], off_key, off_state, off_hist, off_rec, off_err, bytes;
+};
+
+BuildPlan make_plan(int64_t n, int dim);
+
+inline size_t finish_smem_bytes(int ncol) {
+    return (size_t)ncol * kFinishT * 4 + (size_t)kFinishT * 4 * 3 + (size_t)kFinishT * 2;
+}
+
+}  // namespace kd

@@ -1,0 +1,86 @@
+"""kd::build — tree construction (reference kdtree_sequential.cpp:30-70)."""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from .._lib import KdError, check, lib
+from ._util import as_points, ptr, stream_ptr
+
+
+def build_workspace_bytes(n: int, dim: int) -> int:
+    return int(lib().kd_build_workspace_bytes(int(n), int(dim)))
+
+
+def last_launch_count() -> int:
+    """Kernel launches issued by the last GPU build on this thread."""
+    return int(lib().kd_last_launch_count())
+
+
+def build_into(points: torch.Tensor, perm: torch.Tensor, tree_points: torch.Tensor | None,
+               workspace: torch.Tensor | None = None, verify: bool = False) -> None:
+    """Builds into caller-provided outputs (no allocation when ``workspace`` is given)."""
+    points = as_points(points)
+    n, dim = points.shape
+    if points.is_cuda:
+        need = build_workspace_bytes(n, dim)
+        if workspace is None:
+            workspace = torch.empty(need, dtype=torch.uint8, device=points.device)
+        if workspace.numel() * workspace.element_size() < need or workspace.device != points.device:
+            raise KdError(f"kd::build workspace needs {need} bytes on {points.device}")
+        with torch.cuda.device(points.device):
+            check(lib().kd_build_gpu(points.data_ptr(), n, dim, perm.data_ptr(), ptr(tree_points),
+                                     workspace.data_ptr(), workspace.numel() * workspace.element_size(),
+                                     stream_ptr(points.device)), "kd::build")
+            if verify:
+                check(lib().kd_build_status(workspace.data_ptr(), n, dim, stream_ptr(points.device)), "kd::build")
+    else:
+        check(lib().kd_build_cpu(points.data_ptr(), n, dim, perm.data_ptr(), 0), "kd::build")
+        if tree_points is not None:
+            torch.index_select(points, 0, perm.long(), out=tree_points)
+
+
+@torch.library.custom_op("kd::build", mutates_args=())
+def _build_op(points: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
+    points = as_points(points)
+    n, dim = points.shape
+    perm = torch.empty(n, dtype=torch.int32, device=points.device)
+    tree_points = torch.empty((n, dim), dtype=torch.float32, device=points.device)
+    build_into(points, perm, tree_points, verify=True)
+    return perm, tree_points
+
+
+@_build_op.register_fake
+def _(points):
+    n, dim = points.shape
+    return points.new_empty(n, dtype=torch.int32), points.new_empty((n, dim))
+
+
+def build(points: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
+    """Returns ``(perm, tree_points)``.
+
+    ``perm`` (int32[n]) is the tree in in-order layout: the node of range ``[lo, lo+n)`` is
+    ``perm[lo + n//2]``, its sub-trees are ``[lo, lo+n//2)`` and ``[lo+n//2+1, lo+n)``
+    (kdtree_sequential.cpp:51-56).  ``tree_points[s] = points[perm[s]]``.
+    """
+    return torch.ops.kd.build(points)
+
+
+def build_cpu_sortref(points: torch.Tensor) -> torch.Tensor:
+    """The reference's own formulation (sort the first n-1, take n/2) under the (coord, index) order."""
+    points = as_points(points).cpu()
+    n, dim = points.shape
+    perm = torch.empty(n, dtype=torch.int32)
+    check(lib().kd_build_cpu_sortref(points.data_ptr(), n, dim, perm.data_ptr()), "build_cpu_sortref")
+    return perm
+
+
+def check_tree(points: torch.Tensor, perm: torch.Tensor) -> int:
+    """Number of violations of the reference's construction rule in ``perm`` (0 = the unique correct tree)."""
+    points = as_points(points).cpu()
+    perm = perm.to("cpu", torch.int32).contiguous()
+    bad = C.c_int64(0)
+    check(lib().kd_check_tree_cpu(points.data_ptr(), points.shape[0], points.shape[1], perm.data_ptr(),
+                                  C.addressof(bad)), "check_tree")
+    return int(bad.value)

@@ -1,0 +1,112 @@
+"""kd::nearest and friends (reference kdtree_sequential.cpp:75-136, Node.hpp:35-45)."""
+from __future__ import annotations
+
+import torch
+
+from .._lib import check, lib
+from ._util import as_points, stream_ptr
+
+
+@torch.library.custom_op("kd::nearest", mutates_args=())
+def _nearest_op(tree_points: torch.Tensor, perm: torch.Tensor,
+                queries: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
+    tree_points = as_points(tree_points, "tree_points")
+    queries = as_points(queries, "queries")
+    n, dim = tree_points.shape
+    if queries.shape[1] != dim:
+        # the reference exits with "Dimensions do not match!" (kdtree_sequential.cpp:15-18)
+        raise ValueError("Dimensions do not match!")
+    nq = queries.shape[0]
+    dev = tree_points.device
+    perm = perm.to(torch.int32).contiguous()
+    idx = torch.empty(nq, dtype=torch.int32, device=dev)
+    d2 = torch.empty(nq, dtype=torch.float32, device=dev)
+    d = torch.empty(nq, dtype=torch.float32, device=dev)
+    if tree_points.is_cuda:
+        vis = torch.empty(nq, dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            check(lib().kd_nearest_gpu(tree_points.data_ptr(), perm.data_ptr(), n, dim, queries.data_ptr(), nq,
+                                       idx.data_ptr(), d2.data_ptr(), d.data_ptr(), vis.data_ptr(),
+                                       stream_ptr(dev)), "kd::nearest")
+        vis = vis.long()
+    else:
+        # the CPU core indexes the original rows through perm; tree_points[s] == points[perm[s]]
+        vis = torch.empty(nq, dtype=torch.int64)
+        ident = torch.arange(n, dtype=torch.int32)
+        slot = torch.empty(nq, dtype=torch.int32)
+        check(lib().kd_nearest_cpu(tree_points.data_ptr(), n, dim, ident.data_ptr(), queries.data_ptr(), nq,
+                                   slot.data_ptr(), d2.data_ptr(), d.data_ptr(), vis.data_ptr()), "kd::nearest")
+        idx = perm[slot.long()]
+    return idx, d2, d, vis
+
+
+@_nearest_op.register_fake
+def _(tree_points, perm, queries):
+    nq = queries.shape[0]
+    return (queries.new_empty(nq, dtype=torch.int32), queries.new_empty(nq), queries.new_empty(nq),
+            queries.new_empty(nq, dtype=torch.int64))
+
+
+def nearest(tree_points: torch.Tensor, perm: torch.Tensor, queries: torch.Tensor):
+    """1-NN of every query with the reference's traversal; returns (point index, dist², dist, nodes visited)."""
+    return torch.ops.kd.nearest(tree_points, perm, queries)
+
+
+def gather_rows(points: torch.Tensor, perm: torch.Tensor) -> torch.Tensor:
+    points = as_points(points)
+    if not points.is_cuda:
+        return points.index_select(0, perm.long())
+    out = torch.empty_like(points)
+    with torch.cuda.device(points.device):
+        check(lib().kd_gather_rows_gpu(points.data_ptr(), perm.data_ptr(), points.shape[0], points.shape[1],
+                                       out.data_ptr(), stream_ptr(points.device)), "kd::gather_rows")
+    return out
+
+
+@torch.library.custom_op("kd::materialize_nodes", mutates_args=())
+def _materialize_op(perm: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    perm = perm.to(torch.int32).contiguous()
+    n = perm.numel()
+    node_point, left, right = (torch.empty_like(perm) for _ in range(3))
+    if perm.is_cuda:
+        with torch.cuda.device(perm.device):
+            check(lib().kd_materialize_nodes_gpu(n, perm.data_ptr(), node_point.data_ptr(), left.data_ptr(),
+                                                 right.data_ptr(), stream_ptr(perm.device)), "kd::materialize_nodes")
+    else:
+        check(lib().kd_materialize_nodes_cpu(n, perm.data_ptr(), node_point.data_ptr(), left.data_ptr(),
+                                             right.data_ptr()), "kd::materialize_nodes")
+    return node_point, left, right
+
+
+@_materialize_op.register_fake
+def _(perm):
+    return torch.empty_like(perm), torch.empty_like(perm), torch.empty_like(perm)
+
+
+def materialize_nodes(perm: torch.Tensor):
+    """``Node{point,left,right}`` (Node.hpp:35-45) as int32 arrays indexed by slot; -1 = nullptr; root = n//2."""
+    return torch.ops.kd.materialize_nodes(perm)
+
+
+@torch.library.custom_op("kd::bbox", mutates_args=())
+def _bbox_op(points: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
+    points = as_points(points)
+    if not points.is_cuda:
+        return points.min(0).values, points.max(0).values
+    dim = points.shape[1]
+    mn = torch.empty(dim, dtype=torch.float32, device=points.device)
+    mx = torch.empty(dim, dtype=torch.float32, device=points.device)
+    with torch.cuda.device(points.device):
+        check(lib().kd_bbox_gpu(points.data_ptr(), points.shape[0], dim, mn.data_ptr(), mx.data_ptr(),
+                                stream_ptr(points.device)), "kd::bbox")
+    return mn, mx
+
+
+@_bbox_op.register_fake
+def _(points):
+    return points.new_empty(points.shape[1]), points.new_empty(points.shape[1])
+
+
+def bbox(points: torch.Tensor):
+    """Per-axis (min, max) of a point set."""
+    return torch.ops.kd.bbox(points)

@@ -1,0 +1,87 @@
+"""The reference's I/O contract (Utility.cpp:66-124, drivers) through `python -m parallel_kd_tree_b200`."""
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+
+GOLDEN_SEED1 = """READY
+ID: 500000 \t DISTANCE: 707.539
+ID: 500001 \t DISTANCE: 653.765
+ID: 500002 \t DISTANCE: 693.995
+ID: 500003 \t DISTANCE: 715.386
+ID: 500004 \t DISTANCE: 732.924
+ID: 500005 \t DISTANCE: 702.161
+ID: 500006 \t DISTANCE: 739.194
+ID: 500007 \t DISTANCE: 693.53
+ID: 500008 \t DISTANCE: 698.66
+ID: 500009 \t DISTANCE: 736.767
+DONE
+"""
+
+
+class _Result:
+    def __init__(self, returncode, stdout, stderr):
+        self.returncode, self.stdout, self.stderr = returncode, stdout, stderr
+
+
+def run_cli(args, stdin="", subprocess_mode=False):
+    """Runs the CLI; in-process by default (importing torch in a fresh interpreter takes seconds)."""
+    if subprocess_mode:
+        return subprocess.run([sys.executable, "-m", "parallel_kd_tree_b200", *args], input=stdin,
+                              capture_output=True, text=True, cwd=ROOT)
+    import contextlib
+    import io
+
+    from parallel_kd_tree_b200 import cli
+    out, err = io.StringIO(), io.StringIO()
+    old_stdin = sys.stdin
+    sys.stdin = io.StringIO(stdin)
+    try:
+        with contextlib.redirect_stdout(out), contextlib.redirect_stderr(err):
+            try:
+                code = cli.main(list(args))
+            except SystemExit as e:
+                code = e.code if isinstance(e.code, int) else 1
+    finally:
+        sys.stdin = old_stdin
+    return _Result(code, out.getvalue(), err.getvalue())
+
+
+def test_argv_mode_matches_reference_lines(oracle):
+    r = run_cli(["sequential", "--device", "cpu", "7", "3", "5000"])
+    assert r.returncode == 0
+    out = r.stdout.splitlines()
+    assert out[0] == "READY" and out[-1] == "DONE" and out[-2].startswith("elapsed time ")
+    assert "\n".join(out[1:11]) + "\n" == oracle.lines("seed:7", 3, 5000, 10)
+    assert "\tUsing seed 7\n\tUsing point dimensions 3\n\tUsing number of points 5000\n\n" in r.stderr
+
+
+def test_usage_and_validation_errors():
+    r = run_cli(["sequential", "--device", "cpu", "1", "2"])
+    assert r.returncode == 1 and "Usage: sequential SEED DIM_POINTS  NUM_POINTS" in r.stderr
+    r = run_cli(["sequential", "--device", "cpu", "-4", "2", "10"])
+    assert r.returncode == 1 and "Seed has to be larger than 0!" in r.stderr and r.stdout == "READY\n"
+    r = run_cli(["sequential", "--device", "cpu", "0", "0", "10"])
+    assert r.returncode == 1 and "Warning: default value 0 used as seed." in r.stderr
+    assert "Dimension has to be larger than 0!" in r.stderr
+    r = run_cli(["sequential", "--device", "cpu", "1", "2", "0"])
+    assert r.returncode == 1 and "Number of points has to be larger than 0!" in r.stderr
+
+
+def test_mpi_argv_mode_matches_forest_emulation(oracle):
+    r = run_cli(["mpi", "--device", "cpu", "--world", "4", "3", "3", "4001"])
+    assert r.returncode == 0
+    out = r.stdout.splitlines()
+    assert "\n".join(out[1:11]) + "\n" == oracle.forest_lines(3, 3, 4001, 10, 4)
+
+
+@pytest.mark.slow
+def test_default_problem_stdin_seed_golden_lines():
+    # the graded problem: 500000 x 128, seed on stdin (PDF p.4); golden lines = unmodified ./sequential, BASELINE.md
+    r = run_cli(["sequential", "--device", "cpu"], stdin="1\n", subprocess_mode=True)
+    assert r.returncode == 0
+    assert r.stdout == GOLDEN_SEED1
+    assert r.stderr.startswith("Specify seed \tUsing seed 1\n")
