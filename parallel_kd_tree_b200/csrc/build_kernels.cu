@@ -86,7 +86,7 @@ __device__ __forceinline__ void warp_hist_add(unsigned* sh, unsigned digit, bool
     if (valid && (__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&sh[digit], __popc(peers));
 }
 
-template <int BLOCK>
+template <int BLOCK, int UNROLL>
 __global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys, const int32_t* __restrict__ idx,
                                                 const SegState* __restrict__ st, unsigned* __restrict__ ghist,
                                                 unsigned N, int level, int cps, int d) {
@@ -104,30 +104,41 @@ __global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys, 
     __syncthreads();
     const int dsh = digit_shift(d);
     const unsigned mask = (1u << digit_bits(d)) - 1u;
-    unsigned iters = (e - b + BLOCK - 1) / BLOCK;
+    const unsigned iters = (e - b + BLOCK * UNROLL - 1) / (BLOCK * UNROLL);
     if (d < 3) {
         const int ks = dsh - 32;
         const int ps = d == 0 ? 0 : digit_shift(d - 1) - 32;
         const unsigned want = d == 0 ? 0u : (unsigned)(S.prefix >> digit_shift(d - 1));
         for (unsigned it = 0; it < iters; ++it) {
-            unsigned i = b + it * BLOCK + threadIdx.x;
-            bool valid = i < e;
-            unsigned key = valid ? ordered_key(keys[i]) : 0u;
-            if (d > 0) valid = valid && ((key >> ps) == want);
-            warp_hist_add(sh, (key >> ks) & mask, valid);
+            unsigned i0 = b + it * (BLOCK * UNROLL) + threadIdx.x;
+            float f[UNROLL];
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) f[u] = (i0 + u * BLOCK) < e ? keys[i0 + u * BLOCK] : 0.f;
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) {
+                bool valid = (i0 + u * BLOCK) < e;
+                unsigned key = ordered_key(f[u]);
+                if (d > 0) valid = valid && ((key >> ps) == want);
+                warp_hist_add(sh, (key >> ks) & mask, valid);
+            }
         }
     } else {
         const unsigned wantkey = (unsigned)(S.prefix >> 32);
         const int ps = d == 3 ? 0 : digit_shift(d - 1);
         const unsigned wantidx = d == 3 ? 0u : ((unsigned)(S.prefix & 0xffffffffull) >> ps);
         for (unsigned it = 0; it < iters; ++it) {
-            unsigned i = b + it * BLOCK + threadIdx.x;
-            bool valid = i < e;
-            unsigned key = valid ? ordered_key(keys[i]) : 0u;
-            valid = valid && key == wantkey;
-            unsigned id = valid ? (unsigned)idx[i] : 0u;
-            if (d > 3) valid = valid && ((id >> ps) == wantidx);
-            warp_hist_add(sh, (id >> dsh) & mask, valid);
+            unsigned i0 = b + it * (BLOCK * UNROLL) + threadIdx.x;
+            float f[UNROLL];
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) f[u] = (i0 + u * BLOCK) < e ? keys[i0 + u * BLOCK] : 0.f;
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) {
+                unsigned i = i0 + u * BLOCK;
+                bool valid = i < e && ordered_key(f[u]) == wantkey;
+                unsigned id = valid ? (unsigned)idx[i] : 0u;
+                if (d > 3) valid = valid && ((id >> ps) == wantidx);
+                warp_hist_add(sh, (id >> dsh) & mask, valid);
+            }
         }
     }
     __syncthreads();
@@ -195,8 +206,8 @@ __global__ void __launch_bounds__(256) k_scan(SegState* st, unsigned* ghist, int
 // ------------------------------------------------------------------------------------------
 struct MaxRec { unsigned long long comp; unsigned pos; unsigned valid; };
 
-template <int BLOCK, int IPT>
-__global__ void __launch_bounds__(BLOCK) k_partition(Cols src, Cols dst, int ncol, const float* __restrict__ keys,
+template <int NCOL, int BLOCK, int IPT>
+__global__ void __launch_bounds__(BLOCK) k_partition(Cols src, Cols dst, const float* __restrict__ keys, int axis,
                                                      SegState* st, MaxRec* rec, int32_t* __restrict__ perm,
                                                      float* __restrict__ tree_pts, int dim, unsigned N, int level,
                                                      int cps) {
@@ -218,24 +229,39 @@ __global__ void __launch_bounds__(BLOCK) k_partition(Cols src, Cols dst, int nco
 
     if (j == (unsigned)cps - 1 && tid == 0) {  // the pinned element keeps its slot: last of the right range
         unsigned p = lo + n - 1;
-        for (int c = 0; c < ncol; ++c) dst.c[c][p] = src.c[c][p];
+#pragma unroll
+        for (int c = 0; c < NCOL; ++c) dst.c[c][p] = src.c[c][p];
         dst.idx[p] = src.idx[p];
     }
     for (unsigned tb = b; tb < e; tb += BLOCK * IPT) {
         if (tid < 2) s_cnt[tid] = 0;
         __syncthreads();
-        unsigned key[IPT], rk[IPT];
+        // every column of the tile goes to registers first: the loads overlap the ranking below
+        float val[IPT][NCOL > 0 ? NCOL : 1];
+        float kf[IPT];
         int id[IPT];
+        unsigned rk[IPT];
         signed char side[IPT];  // -1 left, 0 node, 1 right, 2 nothing
 #pragma unroll
         for (int k = 0; k < IPT; ++k) {
             unsigned i = tb + k * BLOCK + tid;
             bool valid = i < e;
-            key[k] = valid ? ordered_key(keys[i]) : 0u;
             id[k] = valid ? src.idx[i] : 0;
+#pragma unroll
+            for (int c = 0; c < NCOL; ++c) val[k][c] = valid ? src.c[c][i] : 0.f;
+            if (NCOL == 0) kf[k] = valid ? keys[i] : 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < IPT; ++k) {
+            unsigned i = tb + k * BLOCK + tid;
+            if (NCOL > 0) {
+                kf[k] = val[k][0];
+#pragma unroll
+                for (int c = 1; c < NCOL; ++c) kf[k] = (c == axis) ? val[k][c] : kf[k];
+            }
             side[k] = 2;
-            if (valid) {
-                unsigned long long c = composite(key[k], (unsigned)id[k]) >> shift;
+            if (i < e) {
+                unsigned long long c = composite(ordered_key(kf[k]), (unsigned)id[k]) >> shift;
                 side[k] = c < want ? -1 : (c > want ? 1 : 0);
             }
         }
@@ -262,20 +288,22 @@ __global__ void __launch_bounds__(BLOCK) k_partition(Cols src, Cols dst, int nco
         const unsigned baseL = lo + s_base[0], baseR = lo + m + 1 + s_base[1];
 #pragma unroll
         for (int k = 0; k < IPT; ++k) {
-            unsigned i = tb + k * BLOCK + tid;
             if (side[k] == 2) continue;
             if (side[k] == 0) {
                 // the node of this range: final slot lo + n/2 (kdtree_sequential.cpp:51,65)
                 perm[lo + m] = id[k];
-                if (tree_pts && ncol)
-                    for (int c = 0; c < ncol; ++c) tree_pts[(size_t)(lo + m) * dim + c] = src.c[c][i];
+                if (tree_pts) {
+#pragma unroll
+                    for (int c = 0; c < NCOL; ++c) tree_pts[(size_t)(lo + m) * dim + c] = val[k][c];
+                }
                 continue;
             }
             unsigned p = (side[k] == -1 ? baseL : baseR) + rk[k];
-            for (int c = 0; c < ncol; ++c) dst.c[c][p] = src.c[c][i];
+#pragma unroll
+            for (int c = 0; c < NCOL; ++c) dst.c[c][p] = val[k][c];
             dst.idx[p] = id[k];
             if (side[k] == -1) {
-                unsigned long long c = composite(key[k], (unsigned)id[k]);
+                unsigned long long c = composite(ordered_key(kf[k]), (unsigned)id[k]);
                 if (!bestvalid || c > best) { best = c; bestpos = p; bestvalid = 1; }
             }
         }
@@ -333,26 +361,59 @@ __global__ void __launch_bounds__(256) k_fixup(Cols dst, int ncol, const MaxRec*
 
 // ------------------------------------------------------------------------------------------
 // K4: finisher.  One CTA owns a range of n <= kFinishT points and builds its whole sub-tree
-// in shared memory: per sub-level a segmented bitonic sort of every sub-range's first n-1
-// positions (the reference's formulation, kdtree_sequential.cpp:46-56), points stay put and
-// a (key, slot) pair moves.  All slots are final at the end and are written out once.
+// in shared memory.  Per sub-level every sub-range's first n-1 positions are sorted on the
+// sub-level's axis (the reference's own formulation, kdtree_sequential.cpp:46-56) by ONE
+// bitonic network over 4096 virtual positions (sub-range s owns the P-aligned block s, padded
+// with +inf): each thread keeps 8 consecutive virtual positions in registers, partners at
+// distance < 8 are exchanged in registers, < 256 with warp shuffles, the few larger ones through
+// shared memory.  Points never move, a (key, slot) pair does; all slots are final at the end and
+// are written out once, coalesced.
 // ------------------------------------------------------------------------------------------
 constexpr int kFinishBlock = 512;
+constexpr int kFinishEpt = kFinishT / kFinishBlock;
+constexpr unsigned kInfKey = 0xffffffffu, kInfSlot = 0xffffu;
+static_assert(kFinishEpt == 8, "the finisher network is written for 8 elements per thread");
 
-__global__ void __launch_bounds__(kFinishBlock) k_finish(Cols src, int ncol, const float* __restrict__ pts, int dim,
-                                                         unsigned N, int level, int32_t* __restrict__ perm,
-                                                         float* __restrict__ tree_pts) {
+__device__ __forceinline__ bool fin_less(unsigned ak, unsigned as, unsigned bk, unsigned bs,
+                                         const int32_t* __restrict__ sidx) {
+    if (ak != bk) return ak < bk;
+    if (as == kInfSlot) return false;  // padding sorts last
+    if (bs == kInfSlot) return true;
+    return sidx[as] < sidx[bs];        // equal coordinates: the point index decides
+}
+
+template <int S>
+__device__ __forceinline__ void fin_reg_step(unsigned (&key)[8], unsigned (&slot)[8], unsigned vbase, unsigned k,
+                                             bool last, const int32_t* __restrict__ sidx) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        if (e & S) continue;
+        const int f = e | S;
+        const bool asc = last || (((vbase + e) & k) == 0u);
+        const bool sw = asc ? fin_less(key[f], slot[f], key[e], slot[e], sidx)
+                            : fin_less(key[e], slot[e], key[f], slot[f], sidx);
+        if (sw) {
+            unsigned t = key[e]; key[e] = key[f]; key[f] = t;
+            t = slot[e]; slot[e] = slot[f]; slot[f] = t;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, const float* __restrict__ pts,
+                                                            int dim, unsigned N, int level,
+                                                            int32_t* __restrict__ perm, float* __restrict__ tree_pts) {
     extern __shared__ __align__(16) unsigned char smem[];
     constexpr int T = kFinishT;
     unsigned lo, n;
     seg_range(N, level, blockIdx.x, lo, n);
     if (n == 0) return;
-    float* scol = reinterpret_cast<float*>(smem);                      // [ncol][T]  coordinates by slot
-    int32_t* sidx = reinterpret_cast<int32_t*>(scol + (size_t)ncol * T);  // [T]     point index by slot
-    unsigned* skey = reinterpret_cast<unsigned*>(sidx + T);            // [T]        sort key by position
-    unsigned* stab = skey + T;                                         // [T]        sub-range table (lo << 16 | n)
-    unsigned short* sord = reinterpret_cast<unsigned short*>(stab + T);  // [T]      slot by position
-    const int tid = threadIdx.x;
+    float* scol = reinterpret_cast<float*>(smem);                         // [ncol][T]  coordinates by slot
+    int32_t* sidx = reinterpret_cast<int32_t*>(scol + (size_t)ncol * T);  // [T]        point index by slot
+    unsigned* xkey = reinterpret_cast<unsigned*>(sidx + T);               // [T]        exchange buffer (keys)
+    unsigned* stab = xkey + T;                                            // [T/2]      sub-range table (lo << 16 | n)
+    unsigned short* sord = reinterpret_cast<unsigned short*>(stab + T / 2);  // [T]     slot by position
+    unsigned short* xslot = sord + T;                                     // [T]        exchange buffer (slots)
+    const unsigned tid = threadIdx.x;
     for (unsigned p = tid; p < n; p += kFinishBlock) {
         sidx[p] = src.idx[lo + p];
         for (int c = 0; c < ncol; ++c) scol[c * T + p] = src.c[c][lo + p];
@@ -360,66 +421,80 @@ __global__ void __launch_bounds__(kFinishBlock) k_finish(Cols src, int ncol, con
     }
     if (tid == 0) stab[0] = n;  // sub-range 0 of sub-level 0: lo = 0, size n
     __syncthreads();
+    const unsigned vbase = tid * 8u;
     for (int j = 0; (n >> j) >= 3u; ++j) {
         const unsigned nsub = 1u << j;
         const int axis = (level + j) % dim;
-        for (unsigned p = tid; p < n; p += kFinishBlock) {
-            unsigned slot = sord[p];
-            float f = ncol ? scol[axis * T + slot] : pts[(size_t)sidx[slot] * dim + axis];
-            skey[p] = ordered_key(f);
-        }
-        __syncthreads();
-        unsigned maxsort = (n >> j) - 1u;  // the left-most sub-range is the largest
+        const unsigned maxsort = (n >> j) - 1u;  // the left-most sub-range is the largest
         unsigned P = 2;
-        int logHalf = 0;
-        while (P < maxsort) { P <<= 1; ++logHalf; }
-        const unsigned halfP = P >> 1, total = nsub << logHalf;
+        int logP = 1;
+        while (P < maxsort) { P <<= 1; ++logP; }
+        unsigned key[8], slot[8], pos[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const unsigned v = vbase + e, sub = v >> logP, i = v & (P - 1u);
+            const unsigned tb = sub < nsub ? stab[sub] : 0u;
+            const unsigned sn = tb & 0xffffu, slo = tb >> 16;
+            key[e] = kInfKey;
+            slot[e] = kInfSlot;
+            pos[e] = 0xffffffffu;
+            if (sn >= 3u && i + 1u < sn) {  // position i of the sub-range's first n-1 (the last slot is pinned)
+                pos[e] = slo + i;
+                slot[e] = sord[pos[e]];
+                const float f = ncol ? scol[axis * T + slot[e]] : pts[(size_t)sidx[slot[e]] * dim + axis];
+                key[e] = ordered_key(f);
+            }
+        }
         for (unsigned k = 2; k <= P; k <<= 1) {
-            int ljj = 31 - __clz(k >> 1);
-            for (unsigned jj = k >> 1; jj >= 1; jj >>= 1, --ljj) {
-                const bool flip = jj == (k >> 1);
-                for (unsigned t = tid; t < total; t += kFinishBlock) {
-                    unsigned sub = t >> logHalf, w = t & (halfP - 1u);
-                    unsigned tb = stab[sub];
-                    unsigned sn = tb & 0xffffu, slo = tb >> 16;
-                    if (sn < 3u) continue;
-                    unsigned sz = sn - 1u;
-                    unsigned i, l;
-                    const unsigned g = w >> ljj, r = w & (jj - 1u);
-                    if (flip) {
-                        i = g * k + r;
-                        l = g * k + (k - 1u - r);
-                    } else {
-                        i = g * 2u * jj + r;
-                        l = i + jj;
-                    }
-                    if (l >= sz) continue;
-                    unsigned a = slo + i, bb = slo + l;
-                    unsigned ka = skey[a], kb = skey[bb];
-                    bool sw = ka > kb;
-                    if (ka == kb) sw = sidx[sord[a]] > sidx[sord[bb]];
-                    if (sw) {
-                        skey[a] = kb;
-                        skey[bb] = ka;
-                        unsigned short oa = sord[a];
-                        sord[a] = sord[bb];
-                        sord[bb] = oa;
-                    }
+            const bool last = k == P;  // the final merge of every sub-range is ascending
+            unsigned s = k >> 1;
+            for (; s >= 256u; s >>= 1) {  // partner in another warp: through shared memory
+#pragma unroll
+                for (int e = 0; e < 8; ++e) { xkey[e * kFinishBlock + tid] = key[e]; xslot[e * kFinishBlock + tid] = (unsigned short)slot[e]; }
+                __syncthreads();
+                const unsigned d = s >> 3, pt = tid ^ d;
+                const bool keep_min = ((tid & d) == 0u) == (last || ((vbase & k) == 0u));
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const unsigned ok = xkey[e * kFinishBlock + pt], os = xslot[e * kFinishBlock + pt];
+                    const bool take = keep_min ? fin_less(ok, os, key[e], slot[e], sidx)
+                                               : fin_less(key[e], slot[e], ok, os, sidx);
+                    if (take) { key[e] = ok; slot[e] = os; }
                 }
                 __syncthreads();
             }
+            for (; s >= 8u; s >>= 1) {  // partner in the same warp
+                const unsigned d = s >> 3;
+                const bool keep_min = ((tid & d) == 0u) == (last || ((vbase & k) == 0u));
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const unsigned ok = __shfl_xor_sync(0xffffffffu, key[e], d);
+                    const unsigned os = __shfl_xor_sync(0xffffffffu, slot[e], d);
+                    const bool take = keep_min ? fin_less(ok, os, key[e], slot[e], sidx)
+                                               : fin_less(key[e], slot[e], ok, os, sidx);
+                    if (take) { key[e] = ok; slot[e] = os; }
+                }
+            }
+            if (s == 4u) { fin_reg_step<4>(key, slot, vbase, k, last, sidx); s = 2u; }
+            if (s == 2u) { fin_reg_step<2>(key, slot, vbase, k, last, sidx); s = 1u; }
+            fin_reg_step<1>(key, slot, vbase, k, last, sidx);
         }
-        // next sub-level's table: range s -> 2s (left n/2) and 2s+1 (right n-n/2-1), node slot drops out
-        unsigned ent[(T / 4 + kFinishBlock - 1) / kFinishBlock + 1];
-        int cnt = 0;
-        for (unsigned sidx2 = tid; sidx2 < nsub; sidx2 += kFinishBlock) ent[cnt++] = stab[sidx2];
-        __syncthreads();
-        cnt = 0;
-        for (unsigned sidx2 = tid; sidx2 < nsub; sidx2 += kFinishBlock) {
-            unsigned tb = ent[cnt++];
-            unsigned sn = tb & 0xffffu, slo = tb >> 16, m = sn >> 1;
-            stab[2 * sidx2] = (slo << 16) | m;
-            stab[2 * sidx2 + 1] = sn ? (((slo + m + 1u) << 16) | (sn - m - 1u)) : (slo << 16);
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+            if (pos[e] != 0xffffffffu) sord[pos[e]] = (unsigned short)slot[e];
+        // next sub-level's table: range s -> 2s (left n/2) and 2s+1 (right n-n/2-1), the node slot drops out
+        if ((n >> (j + 1)) >= 3u) {
+            unsigned ent[2];
+            int cnt = 0;
+            for (unsigned q = tid; q < nsub; q += kFinishBlock) ent[cnt++] = stab[q];
+            __syncthreads();
+            cnt = 0;
+            for (unsigned q = tid; q < nsub; q += kFinishBlock) {
+                const unsigned tb = ent[cnt++];
+                const unsigned sn = tb & 0xffffu, slo = tb >> 16, m = sn >> 1;
+                stab[2 * q] = (slo << 16) | m;
+                stab[2 * q + 1] = sn ? (((slo + m + 1u) << 16) | (sn - m - 1u)) : (slo << 16);
+            }
         }
         __syncthreads();
     }
@@ -542,13 +617,26 @@ int build_gpu(const float* points, int64_t n, int dim, int32_t* perm, float* tre
             keys = keybuf;
         }
         for (int d = 0; d < kNumDigits; ++d) {
-            k_hist<512><<<(unsigned)(nseg * cps_h), 512, 0, stream>>>(keys, buf[cur].idx, st, ghist, N, level, cps_h, d);
+            k_hist<512, 4><<<(unsigned)(nseg * cps_h), 512, 0, stream>>>(keys, buf[cur].idx, st, ghist, N, level, cps_h, d);
             KD_LAUNCH_CHECK("k_hist");
             k_scan<<<(unsigned)nseg, 256, 0, stream>>>(st, ghist, d, err);
             KD_LAUNCH_CHECK("k_scan");
         }
-        k_partition<256, 8><<<(unsigned)(nseg * cps_p), 256, 0, stream>>>(buf[cur], buf[cur ^ 1], p.ncol, keys, st, rec,
-                                                                        perm, tree_points, dim, N, level, cps_p);
+        {
+            constexpr int PB = 512, PI = 4;
+            const unsigned grid = (unsigned)(nseg * cps_p);
+#define KD_PART(NC)                                                                                          \
+    k_partition<NC, PB, PI><<<grid, PB, 0, stream>>>(buf[cur], buf[cur ^ 1], keys, axis, st, rec, perm,     \
+                                                     tree_points, dim, N, level, cps_p)
+            switch (p.ncol) {
+                case 0: KD_PART(0); break;
+                case 1: KD_PART(1); break;
+                case 2: KD_PART(2); break;
+                case 3: KD_PART(3); break;
+                default: KD_PART(4); break;
+            }
+#undef KD_PART
+        }
         KD_LAUNCH_CHECK("k_partition");
         k_fixup<<<(unsigned)((nseg + 7) / 8), 256, 0, stream>>>(buf[cur ^ 1], p.ncol, rec, N, level, (unsigned)nseg,
                                                                cps_p);

@@ -34,7 +34,8 @@ struct BuildPlan {
 BuildPlan make_plan(int64_t n, int dim);
 
 inline size_t finish_smem_bytes(int ncol) {
-    return (size_t)ncol * kFinishT * 4 + (size_t)kFinishT * 4 * 3 + (size_t)kFinishT * 2;
+    // scol[ncol][T] f32, sidx[T] i32, xkey[T] u32, stab[T/2] u32, sord[T] u16, xslot[T] u16
+    return (size_t)ncol * kFinishT * 4 + (size_t)kFinishT * 4 * 2 + (size_t)kFinishT * 2 + (size_t)kFinishT * 2 * 2;
 }
 
 }  // namespace kd
