@@ -374,28 +374,41 @@ constexpr int kFinishEpt = kFinishT / kFinishBlock;
 constexpr unsigned kInfKey = 0xffffffffu, kInfSlot = 0xffffu;
 static_assert(kFinishEpt == 8, "the finisher network is written for 8 elements per thread");
 
-__device__ __forceinline__ bool fin_less(unsigned ak, unsigned as, unsigned bk, unsigned bs,
-                                         const int32_t* __restrict__ sidx) {
-    if (ak != bk) return ak < bk;
-    if (as == kInfSlot) return false;  // padding sorts last
-    if (bs == kInfSlot) return true;
-    return sidx[as] < sidx[bs];        // equal coordinates: the point index decides
+// "other sorts before mine" under (key, point index).  Keys differ almost always; a real tie needs the
+// indices from shared memory and takes the (warp-uniform) slow path.  Padding (kInfKey) never ties.
+__device__ __noinline__ bool fin_tie_before(unsigned as, unsigned bs, const int32_t* sidx) { return sidx[as] < sidx[bs]; }
+
+// compare-exchange against a partner value: keep the smaller (keep_min) or the larger element
+__device__ __forceinline__ void fin_ce_partner(unsigned& key, unsigned& slot, unsigned ok, unsigned os, bool keep_min,
+                                               const int32_t* __restrict__ sidx) {
+    bool take = keep_min ? (ok < key) : (ok > key);
+    const bool tie = (ok == key) && (key != kInfKey);
+    if (__any_sync(0xffffffffu, tie)) {
+        if (tie) take = fin_tie_before(os, slot, sidx) == keep_min;
+    }
+    key = take ? ok : key;
+    slot = take ? os : slot;
 }
 
 template <int S>
 __device__ __forceinline__ void fin_reg_step(unsigned (&key)[8], unsigned (&slot)[8], unsigned vbase, unsigned k,
                                              bool last, const int32_t* __restrict__ sidx) {
+    const bool asc_hi = last || ((vbase & k) == 0u);  // k >= 8: the direction bit lives in the thread index
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
         if (e & S) continue;
         const int f = e | S;
-        const bool asc = last || (((vbase + e) & k) == 0u);
-        const bool sw = asc ? fin_less(key[f], slot[f], key[e], slot[e], sidx)
-                            : fin_less(key[e], slot[e], key[f], slot[f], sidx);
-        if (sw) {
-            unsigned t = key[e]; key[e] = key[f]; key[f] = t;
-            t = slot[e]; slot[e] = slot[f]; slot[f] = t;
+        const bool asc = k >= 8u ? asc_hi : (last || ((e & k) == 0u));
+        bool sw = asc ? (key[f] < key[e]) : (key[f] > key[e]);
+        const bool tie = (key[f] == key[e]) && (key[e] != kInfKey);
+        if (__any_sync(0xffffffffu, tie)) {
+            if (tie) sw = fin_tie_before(slot[f], slot[e], sidx) == asc;
         }
+        const unsigned ke = key[e], kf = key[f], se = slot[e], sf = slot[f];
+        key[e] = sw ? kf : ke;
+        key[f] = sw ? ke : kf;
+        slot[e] = sw ? sf : se;
+        slot[f] = sw ? se : sf;
     }
 }
 
@@ -457,9 +470,7 @@ __global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, 
 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
                     const unsigned ok = xkey[e * kFinishBlock + pt], os = xslot[e * kFinishBlock + pt];
-                    const bool take = keep_min ? fin_less(ok, os, key[e], slot[e], sidx)
-                                               : fin_less(key[e], slot[e], ok, os, sidx);
-                    if (take) { key[e] = ok; slot[e] = os; }
+                    fin_ce_partner(key[e], slot[e], ok, os, keep_min, sidx);
                 }
                 __syncthreads();
             }
@@ -470,9 +481,7 @@ __global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, 
                 for (int e = 0; e < 8; ++e) {
                     const unsigned ok = __shfl_xor_sync(0xffffffffu, key[e], d);
                     const unsigned os = __shfl_xor_sync(0xffffffffu, slot[e], d);
-                    const bool take = keep_min ? fin_less(ok, os, key[e], slot[e], sidx)
-                                               : fin_less(key[e], slot[e], ok, os, sidx);
-                    if (take) { key[e] = ok; slot[e] = os; }
+                    fin_ce_partner(key[e], slot[e], ok, os, keep_min, sidx);
                 }
             }
             if (s == 4u) { fin_reg_step<4>(key, slot, vbase, k, last, sidx); s = 2u; }
