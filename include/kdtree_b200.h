@@ -89,6 +89,37 @@ int kd_materialize_nodes_gpu(int64_t n, const int32_t* perm, int32_t* node_point
 /* per-axis min/max of a point set: out_min[dim], out_max[dim] (device). */
 int kd_bbox_gpu(const float* points, int64_t n, int dim, float* out_min, float* out_max, void* stream);
 
+/* ---- distributed build of ONE global tree over peer memory (new; oracle = the reference's sequential tree,
+ * kdtree_sequential.cpp:30-66; the reference's own multi-rank program only builds W local trees) ----
+ * Every rank owns a "symmetric heap" of kd_dist_heap_bytes() bytes with the same layout; heap[r] is rank r's
+ * heap as addressable from the calling rank (CUDA IPC mapping, or plain pointers for W virtual ranks on one GPU).
+ * The tree arrays live inside the heap at the offsets reported by kd_dist_offsets().  world must be 1, 2, 4 or 8,
+ * dim <= 4. */
+typedef struct {
+    int world, rank, dim, with_tree_points;
+    int64_t n_total;
+    void* heap[8];
+} kd_dist_ctx;
+size_t kd_dist_heap_bytes(int64_t n_total, int dim, int world, int with_tree_points);
+int kd_dist_offsets(int64_t n_total, int dim, int world, int with_tree_points, size_t* perm_off, size_t* tp_off);
+/* loads this rank's slice (rows [first_row, first_row + local_n) of the global point array) into its heap */
+int kd_dist_init(const kd_dist_ctx* ctx, const float* local_points, int64_t local_n, int64_t first_row, void* stream);
+/* one rank's whole build in program order (one process per GPU); `serial` must grow with every build on a heap */
+int kd_dist_run(const kd_dist_ctx* ctx, uint64_t serial, void* stream);
+/* the same build phase by phase, for W virtual ranks driven by one process (posts of all ranks before waits) */
+int kd_dist_phase(const kd_dist_ctx* ctx, int level, int phase, int pass, uint64_t serial, void* stream);
+int kd_dist_local_build(const kd_dist_ctx* ctx, void* stream);
+int kd_dist_done(const kd_dist_ctx* ctx, int post, uint64_t serial, void* stream);
+/* synchronises the stream; non-zero if a device-side check or a peer wait failed */
+int kd_dist_status(const kd_dist_ctx* ctx, void* stream);
+
+/* ---- symmetric-heap runtime: allocation and CUDA IPC mapping (handle exchange is the caller's job) ---- */
+int kd_symm_alloc(size_t bytes, void** ptr, void* handle64);
+int kd_symm_open(const void* handle64, void** ptr);
+int kd_symm_close(void* ptr);
+int kd_symm_free(void* ptr);
+int kd_symm_memset(void* ptr, size_t bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

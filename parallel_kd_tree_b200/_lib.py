@@ -19,6 +19,12 @@ class KdError(RuntimeError):
     pass
 
 
+class DistCtx(C.Structure):
+    """kd_dist_ctx of include/kdtree_b200.h"""
+    _fields_ = [("world", C.c_int), ("rank", C.c_int), ("dim", C.c_int), ("with_tree_points", C.c_int),
+                ("n_total", C.c_int64), ("heap", C.c_void_p * 8)]
+
+
 def _declare(lib):
     vp, i64, i32, f32 = C.c_void_p, C.c_int64, C.c_int, C.c_float
     sigs = {
@@ -48,6 +54,19 @@ def _declare(lib):
         "kd_gather_rows_gpu": (i32, [vp, vp, i64, i32, vp, vp]),
         "kd_materialize_nodes_gpu": (i32, [i64, vp, vp, vp, vp, vp]),
         "kd_bbox_gpu": (i32, [vp, i64, i32, vp, vp, vp]),
+        "kd_dist_heap_bytes": (C.c_size_t, [i64, i32, i32, i32]),
+        "kd_dist_offsets": (i32, [i64, i32, i32, i32, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+        "kd_dist_init": (i32, [C.POINTER(DistCtx), vp, i64, i64, vp]),
+        "kd_dist_run": (i32, [C.POINTER(DistCtx), C.c_uint64, vp]),
+        "kd_dist_phase": (i32, [C.POINTER(DistCtx), i32, i32, i32, C.c_uint64, vp]),
+        "kd_dist_local_build": (i32, [C.POINTER(DistCtx), vp]),
+        "kd_dist_done": (i32, [C.POINTER(DistCtx), i32, C.c_uint64, vp]),
+        "kd_dist_status": (i32, [C.POINTER(DistCtx), vp]),
+        "kd_symm_alloc": (i32, [C.c_size_t, C.POINTER(vp), vp]),
+        "kd_symm_open": (i32, [vp, C.POINTER(vp)]),
+        "kd_symm_close": (i32, [vp]),
+        "kd_symm_free": (i32, [vp]),
+        "kd_symm_memset": (i32, [vp, C.c_size_t, vp]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(lib, name)   # a missing symbol is a build error, fail loudly

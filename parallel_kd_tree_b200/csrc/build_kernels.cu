@@ -29,16 +29,6 @@
 
 namespace kd {
 
-__device__ __forceinline__ void seg_range(unsigned N, int level, unsigned s, unsigned& lo, unsigned& n) {
-    unsigned l = 0, cnt = N;
-    for (int b = level - 1; b >= 0; --b) {
-        unsigned m = cnt >> 1;
-        if ((s >> b) & 1u) { l += m + 1; cnt = cnt - m - 1; } else { cnt = m; }
-    }
-    lo = l;
-    n = cnt;
-}
-
 // ------------------------------------------------------------------------------------------
 // K1: working columns
 // ------------------------------------------------------------------------------------------
@@ -204,13 +194,11 @@ __global__ void __launch_bounds__(256) k_scan(SegState* st, unsigned* ghist, int
 // K3: partition around the selected element.  Order inside the left / right parts is free
 // (the next level selects under a total order), so output slots are claimed with atomics.
 // ------------------------------------------------------------------------------------------
-struct MaxRec { unsigned long long comp; unsigned pos; unsigned valid; };
 
 template <int NCOL, int BLOCK, int IPT>
 __global__ void __launch_bounds__(BLOCK) k_partition(Cols src, Cols dst, const float* __restrict__ keys, int axis,
-                                                     SegState* st, MaxRec* rec, int32_t* __restrict__ perm,
-                                                     float* __restrict__ tree_pts, int dim, unsigned N, int level,
-                                                     int cps) {
+                                                     SegState* st, MaxRec* rec, OutPtrs out, unsigned out_lo, int dim,
+                                                     unsigned N, int level, int cps) {
     __shared__ unsigned s_cnt[2], s_base[2];
     __shared__ unsigned long long s_wcomp[BLOCK / 32];
     __shared__ unsigned s_wpos[BLOCK / 32];
@@ -291,10 +279,13 @@ __global__ void __launch_bounds__(BLOCK) k_partition(Cols src, Cols dst, const f
             if (side[k] == 2) continue;
             if (side[k] == 0) {
                 // the node of this range: final slot lo + n/2 (kdtree_sequential.cpp:51,65)
-                perm[lo + m] = id[k];
-                if (tree_pts) {
+                // (written to every replica of the tree arrays: the all-gather is part of the store)
+                for (int r = 0; r < out.n; ++r) {
+                    out.perm[r][out_lo + lo + m] = id[k];
+                    if (out.tp[r]) {
 #pragma unroll
-                    for (int c = 0; c < NCOL; ++c) tree_pts[(size_t)(lo + m) * dim + c] = val[k][c];
+                        for (int c = 0; c < NCOL; ++c) out.tp[r][(size_t)(out_lo + lo + m) * dim + c] = val[k][c];
+                    }
                 }
                 continue;
             }
@@ -413,8 +404,8 @@ __device__ __forceinline__ void fin_reg_step(unsigned (&key)[8], unsigned (&slot
 }
 
 __global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, const float* __restrict__ pts,
-                                                            int dim, unsigned N, int level,
-                                                            int32_t* __restrict__ perm, float* __restrict__ tree_pts) {
+                                                            int dim, unsigned N, int level, int depth0,
+                                                            OutPtrs out, unsigned out_lo) {
     extern __shared__ __align__(16) unsigned char smem[];
     constexpr int T = kFinishT;
     unsigned lo, n;
@@ -437,7 +428,7 @@ __global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, 
     const unsigned vbase = tid * 8u;
     for (int j = 0; (n >> j) >= 3u; ++j) {
         const unsigned nsub = 1u << j;
-        const int axis = (level + j) % dim;
+        const int axis = (depth0 + level + j) % dim;
         const unsigned maxsort = (n >> j) - 1u;  // the left-most sub-range is the largest
         unsigned P = 2;
         int logP = 1;
@@ -507,11 +498,16 @@ __global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, 
         }
         __syncthreads();
     }
-    for (unsigned p = tid; p < n; p += kFinishBlock) {
-        unsigned slot = sord[p];
-        perm[lo + p] = sidx[slot];
-        if (tree_pts && ncol)
-            for (int c = 0; c < ncol; ++c) tree_pts[(size_t)(lo + p) * dim + c] = scol[c * T + slot];
+    // every replica of the tree arrays receives this range: the sub-tree all-gather is fused into the store
+    for (int r = 0; r < out.n; ++r) {
+        int32_t* __restrict__ perm = out.perm[r];
+        float* __restrict__ tree_pts = out.tp[r];
+        for (unsigned p = tid; p < n; p += kFinishBlock) {
+            unsigned slot = sord[p];
+            perm[out_lo + lo + p] = sidx[slot];
+            if (tree_pts && ncol)
+                for (int c = 0; c < ncol; ++c) tree_pts[(size_t)(out_lo + lo + p) * dim + c] = scol[c * T + slot];
+        }
     }
 }
 
@@ -569,75 +565,58 @@ static inline int ctas_per_seg(int64_t nseg, int64_t seg_n, int64_t min_chunk) {
         if (e_ != cudaSuccess) return fail(std::string(what) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
-int build_gpu(const float* points, int64_t n, int dim, int32_t* perm, float* tree_points, void* workspace,
-              size_t workspace_bytes, cudaStream_t stream) {
-    if (!points || !perm || !workspace || n <= 0 || dim <= 0) return fail("kd_build_gpu: bad arguments");
-    if (n >= (1ll << 31)) return fail("kd_build_gpu: n must be below 2^31");
-    BuildPlan p = make_plan(n, dim);
-    if (workspace_bytes < p.bytes) return fail("kd_build_gpu: workspace too small");
-    g_launches = 0;
-    const size_t fin_smem = finish_smem_bytes(p.ncol);
+// Builds the sub-tree of one range whose points already sit in buf[cur] (slots 0..n-1): select/partition
+// levels, then the finisher.  `depth0` is the depth of the range's node in the whole tree (it fixes the
+// split axes), `out_lo` the slot of the range's first point in the tree arrays, `out` every replica of
+// the tree arrays that receives the result.
+int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, unsigned out_lo, OutPtrs out,
+               const float* points, BuildScratch sc, cudaStream_t stream) {
+    const size_t fin_smem = finish_smem_bytes(ncol);
     {
         cudaError_t e = cudaFuncSetAttribute(k_finish, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)finish_smem_bytes(kMaxCarry));
-        if (e != cudaSuccess) return fail(std::string("kd_build_gpu: cudaFuncSetAttribute: ") + cudaGetErrorString(e));
+        if (e != cudaSuccess) return fail(std::string("kd build: cudaFuncSetAttribute: ") + cudaGetErrorString(e));
     }
-    unsigned char* ws = (unsigned char*)workspace;
-    Cols buf[2];
-    for (int b = 0; b < 2; ++b) {
-        for (int c = 0; c < kMaxCarry; ++c) buf[b].c[c] = c < p.ncol ? (float*)(ws + p.off_col[b][c]) : nullptr;
-        buf[b].idx = (int32_t*)(ws + p.off_idx[b]);
-    }
-    float* keybuf = p.ncol ? nullptr : (float*)(ws + p.off_key);
-    SegState* st = (SegState*)(ws + p.off_state);
-    unsigned* ghist = (unsigned*)(ws + p.off_hist);
-    MaxRec* rec = (MaxRec*)(ws + p.off_rec);
-    int* err = (int*)(ws + p.off_err);
     const unsigned N = (unsigned)n;
-
-    if (cudaMemsetAsync(ghist, 0, (size_t)p.max_seg * kDigitBins * 4, stream) != cudaSuccess ||
-        cudaMemsetAsync(err, 0, 256, stream) != cudaSuccess)
-        return fail("kd_build_gpu: cudaMemsetAsync failed");
-    k_init<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(points, N, dim, p.ncol, buf[0]);
-    KD_LAUNCH_CHECK("k_init");
-
-    int cur = 0;
+    int finish_level = 0;
+    while ((n >> finish_level) > kFinishT) ++finish_level;
     for (int level = 0;; ++level) {
         const int64_t nseg = 1ll << level;
-        if (level == p.finish_level) {
-            k_finish<<<(unsigned)nseg, kFinishBlock, fin_smem, stream>>>(buf[cur], p.ncol, points, dim, N, level, perm,
-                                                                        tree_points);
+        if (level == finish_level) {
+            k_finish<<<(unsigned)nseg, kFinishBlock, fin_smem, stream>>>(buf[cur], ncol, points, dim, N, level, depth0,
+                                                                        out, out_lo);
             KD_LAUNCH_CHECK("k_finish");
             break;
         }
         const int64_t seg_n = n >> level;
-        const int axis = level % dim;
+        const int axis = (depth0 + level) % dim;
         const int cps_h = ctas_per_seg(nseg, seg_n, 8192);
         const int cps_p = ctas_per_seg(nseg, seg_n, 2048);
-        k_state_init<<<(unsigned)((nseg + 255) / 256), 256, 0, stream>>>(st, N, level, (unsigned)nseg);
+        k_state_init<<<(unsigned)((nseg + 255) / 256), 256, 0, stream>>>(sc.st, N, level, (unsigned)nseg);
         KD_LAUNCH_CHECK("k_state_init");
         const float* keys;
-        if (p.ncol) {
+        if (ncol) {
             keys = buf[cur].c[axis];
         } else {
-            k_gather_keys<<<(unsigned)(nseg * cps_p), 256, 0, stream>>>(points, dim, axis, buf[cur].idx, keybuf, N,
+            k_gather_keys<<<(unsigned)(nseg * cps_p), 256, 0, stream>>>(points, dim, axis, buf[cur].idx, sc.keybuf, N,
                                                                         level, cps_p);
             KD_LAUNCH_CHECK("k_gather_keys");
-            keys = keybuf;
+            keys = sc.keybuf;
         }
         for (int d = 0; d < kNumDigits; ++d) {
-            k_hist<512, 4><<<(unsigned)(nseg * cps_h), 512, 0, stream>>>(keys, buf[cur].idx, st, ghist, N, level, cps_h, d);
+            k_hist<512, 4><<<(unsigned)(nseg * cps_h), 512, 0, stream>>>(keys, buf[cur].idx, sc.st, sc.ghist, N, level,
+                                                                        cps_h, d);
             KD_LAUNCH_CHECK("k_hist");
-            k_scan<<<(unsigned)nseg, 256, 0, stream>>>(st, ghist, d, err);
+            k_scan<<<(unsigned)nseg, 256, 0, stream>>>(sc.st, sc.ghist, d, sc.err);
             KD_LAUNCH_CHECK("k_scan");
         }
         {
             constexpr int PB = 512, PI = 4;
             const unsigned grid = (unsigned)(nseg * cps_p);
-#define KD_PART(NC)                                                                                          \
-    k_partition<NC, PB, PI><<<grid, PB, 0, stream>>>(buf[cur], buf[cur ^ 1], keys, axis, st, rec, perm,     \
-                                                     tree_points, dim, N, level, cps_p)
-            switch (p.ncol) {
+#define KD_PART(NC)                                                                                                \
+    k_partition<NC, PB, PI><<<grid, PB, 0, stream>>>(buf[cur], buf[cur ^ 1], keys, axis, sc.st, sc.rec, out, out_lo, \
+                                                     dim, N, level, cps_p)
+            switch (ncol) {
                 case 0: KD_PART(0); break;
                 case 1: KD_PART(1); break;
                 case 2: KD_PART(2); break;
@@ -647,11 +626,45 @@ int build_gpu(const float* points, int64_t n, int dim, int32_t* perm, float* tre
 #undef KD_PART
         }
         KD_LAUNCH_CHECK("k_partition");
-        k_fixup<<<(unsigned)((nseg + 7) / 8), 256, 0, stream>>>(buf[cur ^ 1], p.ncol, rec, N, level, (unsigned)nseg,
+        k_fixup<<<(unsigned)((nseg + 7) / 8), 256, 0, stream>>>(buf[cur ^ 1], ncol, sc.rec, N, level, (unsigned)nseg,
                                                                cps_p);
         KD_LAUNCH_CHECK("k_fixup");
         cur ^= 1;
     }
+    return 0;
+}
+
+int build_gpu(const float* points, int64_t n, int dim, int32_t* perm, float* tree_points, void* workspace,
+              size_t workspace_bytes, cudaStream_t stream) {
+    if (!points || !perm || !workspace || n <= 0 || dim <= 0) return fail("kd_build_gpu: bad arguments");
+    if (n >= (1ll << 31)) return fail("kd_build_gpu: n must be below 2^31");
+    BuildPlan p = make_plan(n, dim);
+    if (workspace_bytes < p.bytes) return fail("kd_build_gpu: workspace too small");
+    g_launches = 0;
+    unsigned char* ws = (unsigned char*)workspace;
+    Cols buf[2];
+    for (int b = 0; b < 2; ++b) {
+        for (int c = 0; c < kMaxCarry; ++c) buf[b].c[c] = c < p.ncol ? (float*)(ws + p.off_col[b][c]) : nullptr;
+        buf[b].idx = (int32_t*)(ws + p.off_idx[b]);
+    }
+    BuildScratch sc;
+    sc.keybuf = p.ncol ? nullptr : (float*)(ws + p.off_key);
+    sc.st = (SegState*)(ws + p.off_state);
+    sc.ghist = (unsigned*)(ws + p.off_hist);
+    sc.rec = (MaxRec*)(ws + p.off_rec);
+    sc.err = (int*)(ws + p.off_err);
+    const unsigned N = (unsigned)n;
+
+    if (cudaMemsetAsync(sc.ghist, 0, (size_t)p.max_seg * kDigitBins * 4, stream) != cudaSuccess ||
+        cudaMemsetAsync(sc.err, 0, 256, stream) != cudaSuccess)
+        return fail("kd_build_gpu: cudaMemsetAsync failed");
+    k_init<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(points, N, dim, p.ncol, buf[0]);
+    KD_LAUNCH_CHECK("k_init");
+    OutPtrs out{};
+    out.n = 1;
+    out.perm[0] = perm;
+    out.tp[0] = tree_points;
+    if (int rc = build_core(buf, 0, n, dim, p.ncol, 0, 0u, out, points, sc, stream)) return rc;
     if (tree_points && !p.ncol) {
         k_gather_rows<<<148 * 8, 256, 0, stream>>>(points, perm, N, dim, tree_points);
         KD_LAUNCH_CHECK("k_gather_rows");
@@ -659,6 +672,8 @@ int build_gpu(const float* points, int64_t n, int dim, int32_t* perm, float* tre
     return 0;
 }
 
+void count_launch() { ++g_launches; }
+void reset_launches() { g_launches = 0; }
 int64_t last_launches() { return g_launches; }
 
 }  // namespace kd

@@ -24,6 +24,28 @@ struct Cols {
     int32_t* idx;
 };
 
+struct MaxRec {
+    unsigned long long comp;
+    unsigned pos;
+    unsigned valid;
+};
+
+constexpr int kMaxReplicas = 8;
+// Every copy of the tree arrays that receives the build's output (one per GPU in a distributed build).
+struct OutPtrs {
+    int32_t* perm[kMaxReplicas];
+    float* tp[kMaxReplicas];  // may be null
+    int n;
+};
+
+struct BuildScratch {
+    SegState* st;
+    unsigned* ghist;
+    MaxRec* rec;
+    int* err;
+    float* keybuf;  // gather mode only
+};
+
 struct BuildPlan {
     int64_t n;
     int dim, ncol, finish_level;
@@ -32,6 +54,24 @@ struct BuildPlan {
 };
 
 BuildPlan make_plan(int64_t n, int dim);
+
+#if defined(__CUDACC__)
+// Range s of level `level` of a tree over N points: walk the shape rule along the bits of s.
+__device__ __forceinline__ void seg_range(unsigned N, int level, unsigned s, unsigned& lo, unsigned& n) {
+    unsigned l = 0, cnt = N;
+    for (int b = level - 1; b >= 0; --b) {
+        unsigned m = cnt >> 1;
+        if ((s >> b) & 1u) { l += m + 1; cnt = cnt - m - 1; } else { cnt = m; }
+    }
+    lo = l;
+    n = cnt;
+}
+
+int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, unsigned out_lo, OutPtrs out,
+               const float* points, BuildScratch sc, cudaStream_t stream);
+void count_launch();
+void reset_launches();
+#endif
 
 inline size_t finish_smem_bytes(int ncol) {
     // scol[ncol][T] f32, sidx[T] i32, xkey[T] u32, stab[T/2] u32, sord[T] u16, xslot[T] u16

@@ -1,0 +1,872 @@
+// Distributed (multi-GPU) build of ONE global tree over peer memory (NVLink 5 / NVSwitch), no NCCL on
+// the data path.  New scope with respect to the reference: kdtree_mpi.cpp builds W independent local
+// trees (kdtree_mpi.cpp:204-230); here the W GPUs build the tree the reference's *sequential* program
+// builds over all N points (kdtree_sequential.cpp:30-66), bit for bit.
+//
+// The top log2(W) levels span GPUs.  At level l the W ranks form W >> l groups; group g owns range g of
+// that level, spread over its members in member order.  Per level:
+//   K5  k_hist_dist + k_scan_dist   radix select fused with a one-shot P2P reduction: the last CTA of a
+//                                   rank's histogram kernel stores the rank's 2048 bins into a slot in
+//                                   EVERY member's memory and raises a flag there; every member sums the
+//                                   slots and picks the same bin.  No collective call, no host round trip.
+//   K6  k_partition_dist            stream-compaction partition whose stores go straight into the owner
+//                                   GPU's next-level buffers (P2P stores); the node goes to every GPU's
+//                                   tree arrays; per-rank counts are exchanged the same one-shot way.
+//       k_max_*                     the left range's largest element is swapped into its last slot
+//                                   (it is the next pinned element) by the GPU that owns that slot.
+// After the last distributed level every GPU owns one complete sub-range and finishes it with the
+// single-GPU kernels, whose stores are replicated into every GPU's tree arrays (K7: the sub-tree
+// all-gather is fused into the finisher's write-out).
+//
+// Every wait on a peer is a separate tiny kernel from the matching post, so the same code also runs
+// as W *virtual* ranks of one process on one GPU (posts of all ranks are launched before the waits);
+// that is how the logic is tested without a multi-GPU box.  Flags carry a monotonically increasing
+// epoch and are never reset.  Spins give up after ~2 s and record an error instead of hanging the GPU.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdint>
+#include <cstring>
+#include <string>
+
+#include "../../include/kdtree_b200.h"
+#include "build_plan.h"
+#include "kd_common.h"
+#include "kd_error.h"
+
+namespace kd {
+
+constexpr int kMaxWorld = 8;
+enum FlagKind { F_HIST = 0, F_CNT, F_PART, F_MAX, F_FIX, F_DONE, kNumFlagKinds };
+
+struct DistCtl {
+    unsigned long long prefix;
+    unsigned rank_wanted, cnt_global;
+    int shift, done;
+    unsigned my_less;      // local elements already known to sort before the node
+    unsigned mine;         // 1 if this rank holds the node
+    unsigned cnt;          // local element count of the current level
+    unsigned Loff, Roff;   // first left / right output offset of this rank inside the child ranges
+    unsigned curL, curR;   // local partition cursors
+    unsigned ticket;       // last-CTA election of k_hist_dist
+    int err;
+    unsigned pad[3];
+};
+
+struct MaxSlot { unsigned long long comp; unsigned off; unsigned valid; };
+
+struct DistLayout {
+    size_t ctl, flags, hist_slots, lhist, cnt_slots, max_slots, rec, col[2][kMaxCarry], idx[2], perm, tp;
+    size_t st, ghist, lrec, lerr;  // scratch of the local (single-GPU) phase
+    size_t bytes;
+    int64_t cap, max_seg, max_rec;
+};
+
+static DistLayout make_layout(int64_t n_total, int dim, int world, bool with_tp) {
+    DistLayout L{};
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    L.cap = n_total / world + n_total % world + world + 8;
+    L.ctl = take(sizeof(DistCtl));
+    L.flags = take(sizeof(unsigned long long) * kNumFlagKinds * kMaxWorld);
+    L.hist_slots = take((size_t)2 * kMaxWorld * kDigitBins * 4);
+    L.lhist = take((size_t)kDigitBins * 4);
+    L.cnt_slots = take((size_t)kMaxWorld * 4 * 4);
+    L.max_slots = take(sizeof(MaxSlot) * kMaxWorld);
+    L.rec = take(sizeof(MaxRec) * (size_t)(kTargetCtas + 8));
+    for (int b = 0; b < 2; ++b) {
+        for (int c = 0; c < dim; ++c) L.col[b][c] = take((size_t)L.cap * 4);
+        L.idx[b] = take((size_t)L.cap * 4);
+    }
+    L.perm = take((size_t)n_total * 4);
+    L.tp = with_tp ? take((size_t)n_total * dim * 4) : 0;
+    int lv = 0;
+    while ((L.cap >> lv) > kFinishT) ++lv;
+    L.max_seg = lv == 0 ? 1 : (1ll << (lv - 1));
+    L.max_rec = L.max_seg + kTargetCtas;
+    L.st = take((size_t)L.max_seg * sizeof(SegState));
+    L.ghist = take((size_t)L.max_seg * kDigitBins * 4);
+    L.lrec = take((size_t)L.max_rec * sizeof(MaxRec));
+    L.lerr = take(256);
+    L.bytes = off;
+    return L;
+}
+
+struct DistParams {
+    int world, rank, dim, ncol;
+    unsigned N;
+    unsigned char* heap[kMaxWorld];  // this rank's view of every rank's heap
+    DistLayout L;
+};
+
+// geometry of one distributed level, identical on all members of a group
+struct LevelGeo {
+    int level, G, gb, j;   // group size, first rank of my group, my member index
+    unsigned lo, n;        // my group's range
+};
+
+__host__ __device__ inline void host_seg_range(unsigned N, int level, unsigned s, unsigned& lo, unsigned& n) {
+    unsigned l = 0, cnt = N;
+    for (int b = level - 1; b >= 0; --b) {
+        unsigned m = cnt >> 1;
+        if ((s >> b) & 1u) { l += m + 1; cnt = cnt - m - 1; } else { cnt = m; }
+    }
+    lo = l;
+    n = cnt;
+}
+
+__host__ __device__ inline unsigned share_of(unsigned n, unsigned G, unsigned j) { return n / G + (j < n % G ? 1u : 0u); }
+
+// offset o of a range of n elements spread evenly over G members -> (member, local position)
+__device__ __forceinline__ void owner_of(unsigned o, unsigned n, unsigned G, unsigned& member, unsigned& pos) {
+    const unsigned base = n / G, rem = n % G, big = rem * (base + 1u);
+    if (o < big) { member = o / (base + 1u); pos = o - member * (base + 1u); }
+    else { const unsigned o2 = o - big; const unsigned q = o2 / base; member = rem + q; pos = o2 - q * base; }
+}
+
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ bool wait_flag(const unsigned long long* p, unsigned long long epoch) {
+    const long long t0 = clock64();
+    while (ld_acquire_sys(p) < epoch) {
+        if (clock64() - t0 > 4000000000ll) return false;  // ~2 s: give up, never hang the device
+        __nanosleep(64);
+    }
+    return true;
+}
+
+#define DCTL(P, r) (reinterpret_cast<DistCtl*>((P).heap[r] + (P).L.ctl))
+#define DFLAG(P, r, kind, src) (reinterpret_cast<unsigned long long*>((P).heap[r] + (P).L.flags) + (kind) * kMaxWorld + (src))
+
+__device__ __forceinline__ Cols cols_of(const DistParams& P, int r, int b) {
+    Cols c;
+    for (int k = 0; k < kMaxCarry; ++k) c.c[k] = k < P.ncol ? reinterpret_cast<float*>(P.heap[r] + P.L.col[b][k]) : nullptr;
+    c.idx = reinterpret_cast<int32_t*>(P.heap[r] + P.L.idx[b]);
+    return c;
+}
+
+// ------------------------------------------------------------------------------------------------
+__global__ void k_dist_init(DistParams P, const float* __restrict__ pts, unsigned local_n, unsigned first_row) {
+    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    Cols dst = cols_of(P, P.rank, 0);
+    if (i == 0) {
+        DistCtl* c = DCTL(P, P.rank);
+        c->cnt = local_n;
+        c->err = 0;
+        c->ticket = 0;
+    }
+    if (i >= local_n) return;
+    dst.idx[i] = (int32_t)(first_row + i);
+    for (int c = 0; c < P.ncol; ++c) dst.c[c][i] = pts[(size_t)i * P.dim + c];
+}
+
+__global__ void k_dist_state_init(DistParams P, LevelGeo g) {
+    if (threadIdx.x || blockIdx.x) return;
+    DistCtl* c = DCTL(P, P.rank);
+    c->prefix = 0ull;
+    c->rank_wanted = g.n >> 1;
+    c->cnt_global = g.n - 1;
+    c->shift = 64;
+    c->done = 0;
+    c->my_less = 0;
+    c->mine = 0;
+    c->curL = c->curR = 0;
+    c->ticket = 0;
+    if (g.level > 0) c->cnt = share_of(g.n, (unsigned)g.G, (unsigned)g.j);
+}
+
+// K5 (post side): local histogram of digit d; the last CTA to finish publishes the rank's bins to every
+// member of the group and raises their flag.
+__device__ __forceinline__ void warp_hist_add_d(unsigned* sh, unsigned digit, bool valid) {
+    unsigned peers = __match_any_sync(0xffffffffu, valid ? digit : 0xffffffffu);
+    if (valid && (__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&sh[digit], __popc(peers));
+}
+
+template <int BLOCK, int UNROLL>
+__global__ void __launch_bounds__(BLOCK) k_hist_dist(DistParams P, LevelGeo g, int cur, int axis, int d,
+                                                     unsigned long long epoch) {
+    __shared__ unsigned sh[kDigitBins];
+    __shared__ int s_last;
+    DistCtl* ctl = DCTL(P, P.rank);
+    if (ctl->done) return;
+    const unsigned long long prefix = ctl->prefix;
+    const unsigned local_n = ctl->cnt;
+    const unsigned free_n = (g.j == g.G - 1) ? local_n - 1u : local_n;  // the range's pinned last element sits on the last member
+    const Cols src = cols_of(P, P.rank, cur);
+    const float* __restrict__ keys = src.c[axis];
+    const int32_t* __restrict__ idx = src.idx;
+    const unsigned chunk = (free_n + gridDim.x - 1) / gridDim.x;
+    const unsigned b = min(blockIdx.x * chunk, free_n), e = min(b + chunk, free_n);
+    for (int t = threadIdx.x; t < kDigitBins; t += BLOCK) sh[t] = 0;
+    __syncthreads();
+    const int dsh = digit_shift(d);
+    const unsigned mask = (1u << digit_bits(d)) - 1u;
+    const unsigned iters = (e - b + BLOCK * UNROLL - 1) / (BLOCK * UNROLL);
+    const unsigned wantkey = (unsigned)(prefix >> 32);
+    for (unsigned it = 0; it < iters; ++it) {
+        unsigned i0 = b + it * (BLOCK * UNROLL) + threadIdx.x;
+        float f[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) f[u] = (i0 + u * BLOCK) < e ? keys[i0 + u * BLOCK] : 0.f;
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            const unsigned i = i0 + u * BLOCK;
+            bool valid = i < e;
+            const unsigned key = ordered_key(f[u]);
+            unsigned digit;
+            if (d < 3) {
+                if (d > 0) valid = valid && ((key >> (digit_shift(d - 1) - 32)) == (unsigned)(prefix >> digit_shift(d - 1)));
+                digit = (key >> (dsh - 32)) & mask;
+            } else {
+                valid = valid && key == wantkey;
+                const unsigned id = valid ? (unsigned)idx[i] : 0u;
+                if (d > 3) valid = valid && ((id >> digit_shift(d - 1)) == ((unsigned)(prefix & 0xffffffffull) >> digit_shift(d - 1)));
+                digit = (id >> dsh) & mask;
+            }
+            warp_hist_add_d(sh, digit, valid);
+        }
+    }
+    __syncthreads();
+    unsigned* lh = reinterpret_cast<unsigned*>(P.heap[P.rank] + P.L.lhist);
+    for (int t = threadIdx.x; t < kDigitBins; t += BLOCK) {
+        unsigned v = sh[t];
+        if (v) atomicAdd(&lh[t], v);
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&ctl->ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    // one-shot reduction: my bins go to slot (d & 1, my member index) of every member, then their flag
+    for (int t = threadIdx.x; t < kDigitBins; t += BLOCK) {
+        const unsigned v = __ldcg(&lh[t]);
+        lh[t] = 0;
+        for (int m = 0; m < g.G; ++m) {
+            unsigned* slot = reinterpret_cast<unsigned*>(P.heap[g.gb + m] + P.L.hist_slots) +
+                             ((size_t)(d & 1) * kMaxWorld + g.j) * kDigitBins;
+            slot[t] = v;
+        }
+    }
+    if (threadIdx.x == 0) ctl->ticket = 0;
+    __threadfence_system();
+    __syncthreads();
+    if ((int)threadIdx.x < g.G) st_release_sys(DFLAG(P, g.gb + threadIdx.x, F_HIST, g.j), epoch);
+}
+
+// K5 (wait side): sum the members' slots, locate the bin of the wanted rank, extend the prefix.
+__global__ void __launch_bounds__(256) k_scan_dist(DistParams P, LevelGeo g, int d, unsigned long long epoch) {
+    __shared__ unsigned wsum[8];
+    __shared__ int fbin;
+    __shared__ unsigned fcum, fcnt, s_own_less, s_own_at;
+    DistCtl* ctl = DCTL(P, P.rank);
+    if (ctl->done) return;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (tid == 0) { fbin = -1; s_own_less = 0; s_own_at = 0; }
+    if (tid < g.G) {
+        if (!wait_flag(DFLAG(P, P.rank, F_HIST, tid), epoch)) atomicExch(&ctl->err, 100 + d);
+    }
+    __syncthreads();
+    const unsigned* slots = reinterpret_cast<const unsigned*>(P.heap[P.rank] + P.L.hist_slots) +
+                            (size_t)(d & 1) * kMaxWorld * kDigitBins;
+    unsigned v[8], own[8], sum = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        unsigned a = 0;
+        for (int m = 0; m < g.G; ++m) a += __ldcg(&slots[(size_t)m * kDigitBins + tid * 8 + k]);
+        v[k] = a;
+        own[k] = __ldcg(&slots[(size_t)g.j * kDigitBins + tid * 8 + k]);
+        sum += a;
+    }
+    unsigned inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) wsum[w] = inc;
+    __syncthreads();
+    unsigned base = 0;
+    for (int k = 0; k < w; ++k) base += wsum[k];
+    unsigned c = base + inc - sum;
+    const unsigned r = ctl->rank_wanted;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        if (r >= c && r < c + v[k]) { fbin = tid * 8 + k; fcum = c; fcnt = v[k]; }
+        c += v[k];
+    }
+    __syncthreads();
+    const int fb = fbin;
+    unsigned less = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        if (tid * 8 + k < fb) less += own[k];
+        if (tid * 8 + k == fb) s_own_at = own[k];
+    }
+    for (int o = 16; o > 0; o >>= 1) less += __shfl_xor_sync(0xffffffffu, less, o);
+    if (lane == 0 && less) atomicAdd(&s_own_less, less);
+    __syncthreads();
+    if (tid == 0) {
+        if (fb < 0) {
+            atomicExch(&ctl->err, 1 + d);
+            ctl->done = 1;
+        } else {
+            ctl->prefix |= (unsigned long long)(unsigned)fb << digit_shift(d);
+            ctl->rank_wanted = r - fcum;
+            ctl->cnt_global = fcnt;
+            ctl->shift = digit_shift(d);
+            ctl->my_less += s_own_less;
+            if (fcnt == 1u || d == kNumDigits - 1) { ctl->done = 1; ctl->mine = s_own_at; }
+        }
+    }
+}
+
+// per-rank left/right counts -> every member (post), then exclusive scan over members (wait)
+__global__ void k_counts_post(DistParams P, LevelGeo g, unsigned long long epoch) {
+    DistCtl* ctl = DCTL(P, P.rank);
+    const unsigned local_n = ctl->cnt;
+    const unsigned free_n = (g.j == g.G - 1) ? local_n - 1u : local_n;
+    const unsigned lc = ctl->my_less, rc = free_n - lc - ctl->mine;
+    if ((int)threadIdx.x < g.G) {
+        unsigned* slot = reinterpret_cast<unsigned*>(P.heap[g.gb + threadIdx.x] + P.L.cnt_slots) + g.j * 4;
+        slot[0] = lc;
+        slot[1] = rc;
+        __threadfence_system();
+        st_release_sys(DFLAG(P, g.gb + threadIdx.x, F_CNT, g.j), epoch);
+    }
+}
+
+__global__ void k_counts_wait(DistParams P, LevelGeo g, unsigned long long epoch) {
+    DistCtl* ctl = DCTL(P, P.rank);
+    if ((int)threadIdx.x < g.G) {
+        if (!wait_flag(DFLAG(P, P.rank, F_CNT, threadIdx.x), epoch)) atomicExch(&ctl->err, 200);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned* slots = reinterpret_cast<const unsigned*>(P.heap[P.rank] + P.L.cnt_slots);
+        unsigned lo = 0, ro = 0, lt = 0, rt = 0;
+        for (int m = 0; m < g.G; ++m) {
+            const unsigned lc = __ldcg(&slots[m * 4]), rc = __ldcg(&slots[m * 4 + 1]);
+            if (m < g.j) { lo += lc; ro += rc; }
+            lt += lc;
+            rt += rc;
+        }
+        ctl->Loff = lo;
+        ctl->Roff = ro;
+        if (lt != (g.n >> 1) || rt != g.n - (g.n >> 1) - 2u) atomicExch(&ctl->err, 201);
+    }
+}
+
+// K6: partition with P2P stores into the owners' next-level buffers
+template <int NCOL, int BLOCK, int IPT>
+__global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo g, int cur, int axis, bool with_tp) {
+    __shared__ unsigned s_cnt[2], s_base[2];
+    __shared__ unsigned long long s_wcomp[BLOCK / 32];
+    __shared__ unsigned s_wpos[BLOCK / 32];
+    DistCtl* ctl = DCTL(P, P.rank);
+    const int tid = threadIdx.x, lane = tid & 31;
+    const unsigned long long prefix = ctl->prefix;
+    const int shift = ctl->shift;
+    const unsigned long long want = prefix >> shift;
+    const unsigned local_n = ctl->cnt;
+    const bool last_member = g.j == g.G - 1;
+    const unsigned free_n = last_member ? local_n - 1u : local_n;
+    const unsigned m = g.n >> 1, nr = g.n - m - 1u;      // sizes of the child ranges
+    const unsigned Gh = (unsigned)g.G >> 1;              // members per child range
+    const unsigned Loff = ctl->Loff, Roff = ctl->Roff;
+    const Cols src = cols_of(P, P.rank, cur);
+    Cols dst[kMaxWorld];
+    for (int r = 0; r < g.G; ++r) dst[r] = cols_of(P, g.gb + r, cur ^ 1);
+    const unsigned chunk = (free_n + gridDim.x - 1) / gridDim.x;
+    const unsigned b = min(blockIdx.x * chunk, free_n), e = min(b + chunk, free_n);
+    unsigned long long best = 0ull;
+    unsigned bestpos = 0, bestvalid = 0;
+
+    if (last_member && blockIdx.x == gridDim.x - 1 && tid == 0) {
+        // the range's pinned element: last element of the right child range, i.e. of the group's last member
+        const unsigned p = local_n - 1u;
+        unsigned mem, pos;
+        owner_of(nr - 1u, nr, Gh, mem, pos);
+        const Cols& d = dst[Gh + mem];
+#pragma unroll
+        for (int c = 0; c < NCOL; ++c) d.c[c][pos] = src.c[c][p];
+        d.idx[pos] = src.idx[p];
+    }
+    for (unsigned tb = b; tb < e; tb += BLOCK * IPT) {
+        if (tid < 2) s_cnt[tid] = 0;
+        __syncthreads();
+        float val[IPT][NCOL];
+        int id[IPT];
+        unsigned rk[IPT], key[IPT];
+        signed char side[IPT];
+#pragma unroll
+        for (int k = 0; k < IPT; ++k) {
+            unsigned i = tb + k * BLOCK + tid;
+            bool valid = i < e;
+            id[k] = valid ? src.idx[i] : 0;
+#pragma unroll
+            for (int c = 0; c < NCOL; ++c) val[k][c] = valid ? src.c[c][i] : 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < IPT; ++k) {
+            unsigned i = tb + k * BLOCK + tid;
+            float kf = val[k][0];
+#pragma unroll
+            for (int c = 1; c < NCOL; ++c) kf = (c == axis) ? val[k][c] : kf;
+            key[k] = ordered_key(kf);
+            side[k] = 2;
+            if (i < e) {
+                unsigned long long c = composite(key[k], (unsigned)id[k]) >> shift;
+                side[k] = c < want ? -1 : (c > want ? 1 : 0);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < IPT; ++k) {
+            unsigned bl = __ballot_sync(0xffffffffu, side[k] == -1);
+            unsigned br = __ballot_sync(0xffffffffu, side[k] == 1);
+            unsigned wl = 0, wr = 0;
+            if (lane == 0) {
+                if (bl) wl = atomicAdd(&s_cnt[0], __popc(bl));
+                if (br) wr = atomicAdd(&s_cnt[1], __popc(br));
+            }
+            wl = __shfl_sync(0xffffffffu, wl, 0);
+            wr = __shfl_sync(0xffffffffu, wr, 0);
+            unsigned lt = (1u << lane) - 1u;
+            rk[k] = side[k] == -1 ? wl + __popc(bl & lt) : wr + __popc(br & lt);
+        }
+        __syncthreads();
+        if (tid < 2) {
+            unsigned c = s_cnt[tid];
+            s_base[tid] = c ? atomicAdd(tid == 0 ? &ctl->curL : &ctl->curR, c) : 0u;
+        }
+        __syncthreads();
+        const unsigned baseL = Loff + s_base[0], baseR = Roff + s_base[1];
+#pragma unroll
+        for (int k = 0; k < IPT; ++k) {
+            if (side[k] == 2) continue;
+            if (side[k] == 0) {
+                // the node of this range: slot lo + n/2 of every GPU's tree arrays
+                for (int r = 0; r < P.world; ++r) {
+                    reinterpret_cast<int32_t*>(P.heap[r] + P.L.perm)[g.lo + m] = id[k];
+                    if (with_tp) {
+                        float* tp = reinterpret_cast<float*>(P.heap[r] + P.L.tp);
+#pragma unroll
+                        for (int c = 0; c < NCOL; ++c) tp[(size_t)(g.lo + m) * P.dim + c] = val[k][c];
+                    }
+                }
+                continue;
+            }
+            const bool left = side[k] == -1;
+            const unsigned o = (left ? baseL : baseR) + rk[k];
+            unsigned mem, pos;
+            owner_of(o, left ? m : nr, Gh, mem, pos);
+            const Cols& d = dst[left ? mem : Gh + mem];
+#pragma unroll
+            for (int c = 0; c < NCOL; ++c) d.c[c][pos] = val[k][c];
+            d.idx[pos] = id[k];
+            if (left) {
+                unsigned long long c = composite(key[k], (unsigned)id[k]);
+                if (!bestvalid || c > best) { best = c; bestpos = o; bestvalid = 1; }
+            }
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        unsigned long long oc = __shfl_xor_sync(0xffffffffu, best, o);
+        unsigned op = __shfl_xor_sync(0xffffffffu, bestpos, o);
+        unsigned ov = __shfl_xor_sync(0xffffffffu, bestvalid, o);
+        if (ov && (!bestvalid || oc > best)) { best = oc; bestpos = op; bestvalid = 1; }
+    }
+    if (lane == 0) { s_wcomp[tid >> 5] = bestvalid ? best : 0ull; s_wpos[tid >> 5] = bestvalid ? bestpos : 0xffffffffu; }
+    __syncthreads();
+    if (tid == 0) {
+        MaxRec r{0ull, 0u, 0u};
+        for (int w = 0; w < BLOCK / 32; ++w)
+            if (s_wpos[w] != 0xffffffffu && (!r.valid || s_wcomp[w] > r.comp)) { r.comp = s_wcomp[w]; r.pos = s_wpos[w]; r.valid = 1; }
+        reinterpret_cast<MaxRec*>(P.heap[P.rank] + P.L.rec)[blockIdx.x] = r;
+    }
+    __threadfence_system();  // my peer stores are ordered before anything this GPU signals later
+}
+
+// plain group barrier, split in two kernels (see the header comment)
+__global__ void k_flag_post(DistParams P, LevelGeo g, int kind, unsigned long long epoch) {
+    __threadfence_system();
+    if ((int)threadIdx.x < g.G) st_release_sys(DFLAG(P, g.gb + threadIdx.x, kind, g.j), epoch);
+}
+__global__ void k_flag_wait(DistParams P, LevelGeo g, int kind, unsigned long long epoch) {
+    if ((int)threadIdx.x < g.G) {
+        if (!wait_flag(DFLAG(P, P.rank, kind, threadIdx.x), epoch)) atomicExch(&DCTL(P, P.rank)->err, 300 + kind);
+    }
+}
+
+// the left child's largest element -> its last slot.  Post: my best candidate to every member.
+__global__ void __launch_bounds__(256) k_max_post(DistParams P, LevelGeo g, int nrec, unsigned long long epoch) {
+    __shared__ unsigned long long s_c[8];
+    __shared__ unsigned s_p[8], s_v[8];
+    const MaxRec* rec = reinterpret_cast<const MaxRec*>(P.heap[P.rank] + P.L.rec);
+    unsigned long long best = 0ull;
+    unsigned bestpos = 0, bestvalid = 0;
+    for (int t = threadIdx.x; t < nrec; t += blockDim.x) {
+        MaxRec r = rec[t];
+        if (r.valid && (!bestvalid || r.comp > best)) { best = r.comp; bestpos = r.pos; bestvalid = 1; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        unsigned long long oc = __shfl_xor_sync(0xffffffffu, best, o);
+        unsigned op = __shfl_xor_sync(0xffffffffu, bestpos, o);
+        unsigned ov = __shfl_xor_sync(0xffffffffu, bestvalid, o);
+        if (ov && (!bestvalid || oc > best)) { best = oc; bestpos = op; bestvalid = 1; }
+    }
+    if ((threadIdx.x & 31) == 0) { s_c[threadIdx.x >> 5] = best; s_p[threadIdx.x >> 5] = bestpos; s_v[threadIdx.x >> 5] = bestvalid; }
+    __syncthreads();
+    if ((int)threadIdx.x < g.G) {
+        MaxSlot ms{0ull, 0u, 0u};
+        for (int w = 0; w < 8; ++w)
+            if (s_v[w] && (!ms.valid || s_c[w] > ms.comp)) { ms.comp = s_c[w]; ms.off = s_p[w]; ms.valid = 1; }
+        MaxSlot* slot = reinterpret_cast<MaxSlot*>(P.heap[g.gb + threadIdx.x] + P.L.max_slots) + g.j;
+        *slot = ms;
+        __threadfence_system();
+        st_release_sys(DFLAG(P, g.gb + threadIdx.x, F_MAX, g.j), epoch);
+    }
+}
+
+// Wait: the owner of the left child's last slot exchanges it with the winner.
+__global__ void k_max_wait_swap(DistParams P, LevelGeo g, int cur, unsigned long long epoch) {
+    DistCtl* ctl = DCTL(P, P.rank);
+    if ((int)threadIdx.x < g.G) {
+        if (!wait_flag(DFLAG(P, P.rank, F_MAX, threadIdx.x), epoch)) atomicExch(&ctl->err, 400);
+    }
+    __syncthreads();
+    const unsigned m = g.n >> 1, Gh = (unsigned)g.G >> 1;
+    unsigned lastmem, lastpos;
+    owner_of(m - 1u, m, Gh, lastmem, lastpos);
+    if ((unsigned)g.j != lastmem) return;  // only the owner of slot m-1 of the left child acts
+    const MaxSlot* slots = reinterpret_cast<const MaxSlot*>(P.heap[P.rank] + P.L.max_slots);
+    MaxSlot bestm{0ull, 0u, 0u};
+    for (int k = 0; k < g.G; ++k) {
+        MaxSlot s = slots[k];
+        if (s.valid && (!bestm.valid || s.comp > bestm.comp)) bestm = s;
+    }
+    if (!bestm.valid) { if (threadIdx.x == 0) atomicExch(&ctl->err, 401); return; }
+    if (bestm.off == m - 1u) return;
+    unsigned wm, wp;
+    owner_of(bestm.off, m, Gh, wm, wp);
+    Cols a = cols_of(P, g.gb + wm, cur ^ 1), b = cols_of(P, P.rank, cur ^ 1);
+    const int lane = threadIdx.x;
+    if (lane < P.ncol) {
+        float x = a.c[lane][wp], y = b.c[lane][lastpos];
+        a.c[lane][wp] = y;
+        b.c[lane][lastpos] = x;
+    } else if (lane == P.ncol) {
+        int32_t x = a.idx[wp], y = b.idx[lastpos];
+        a.idx[wp] = y;
+        b.idx[lastpos] = x;
+    }
+    __threadfence_system();
+}
+
+__global__ void k_dist_read_err(DistParams P, int* out) { *out = DCTL(P, P.rank)->err; }
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+struct HostCtx {
+    DistParams P;
+    bool with_tp;
+};
+
+static LevelGeo make_geo(const DistParams& P, int level) {
+    LevelGeo g;
+    g.level = level;
+    g.G = P.world >> level;
+    g.gb = (P.rank / g.G) * g.G;
+    g.j = P.rank % g.G;
+    host_seg_range(P.N, level, (unsigned)(P.rank / g.G), g.lo, g.n);
+    return g;
+}
+
+#define KD_DLAUNCH(what)                                                                      \
+    do {                                                                                      \
+        count_launch();                                                                       \
+        cudaError_t e_ = cudaGetLastError();                                                  \
+        if (e_ != cudaSuccess) return fail(std::string(what) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+enum Phase { PH_STATE = 0, PH_HIST, PH_SCAN, PH_CNT_POST, PH_CNT_WAIT, PH_PART, PH_PART_POST, PH_PART_WAIT, PH_MAX_POST,
+             PH_MAX_WAIT, PH_FIX_POST, PH_FIX_WAIT, kNumPhases };
+
+static int dist_grid(unsigned local_n, int min_chunk) {
+    int64_t cap = std::max<int64_t>(1, ((int64_t)local_n + min_chunk - 1) / min_chunk);
+    return (int)std::min<int64_t>(kTargetCtas, cap);
+}
+
+static int run_phase(const HostCtx& H, int level, int phase, int pass, unsigned long long serial, cudaStream_t st) {
+    const DistParams& P = H.P;
+    const LevelGeo g = make_geo(P, level);
+    const int cur = level & 1;
+    const int axis = level % P.dim;
+    const unsigned long long epoch = serial * 64ull + (unsigned long long)level * 8ull + (unsigned long long)pass + 1ull;
+    // upper bound of my local count at this level (the device reads the exact value from its control block)
+    const unsigned local_cap = (unsigned)H.P.L.cap;
+    switch (phase) {
+        case PH_STATE:
+            k_dist_state_init<<<1, 32, 0, st>>>(P, g);
+            KD_DLAUNCH("k_dist_state_init");
+            break;
+        case PH_HIST:
+            k_hist_dist<512, 4><<<dist_grid(local_cap, 16384), 512, 0, st>>>(P, g, cur, axis, pass, epoch);
+            KD_DLAUNCH("k_hist_dist");
+            break;
+        case PH_SCAN:
+            k_scan_dist<<<1, 256, 0, st>>>(P, g, pass, epoch);
+            KD_DLAUNCH("k_scan_dist");
+            break;
+        case PH_CNT_POST:
+            k_counts_post<<<1, 32, 0, st>>>(P, g, epoch);
+            KD_DLAUNCH("k_counts_post");
+            break;
+        case PH_CNT_WAIT:
+            k_counts_wait<<<1, 32, 0, st>>>(P, g, epoch);
+            KD_DLAUNCH("k_counts_wait");
+            break;
+        case PH_PART: {
+            const int grid = dist_grid(local_cap, 2048);
+            switch (P.ncol) {
+                case 1: k_partition_dist<1, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
+                case 2: k_partition_dist<2, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
+                case 3: k_partition_dist<3, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
+                default: k_partition_dist<4, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
+            }
+            KD_DLAUNCH("k_partition_dist");
+            break;
+        }
+        case PH_PART_POST:
+            k_flag_post<<<1, 32, 0, st>>>(P, g, F_PART, epoch);
+            KD_DLAUNCH("k_flag_post");
+            break;
+        case PH_PART_WAIT:
+            k_flag_wait<<<1, 32, 0, st>>>(P, g, F_PART, epoch);
+            KD_DLAUNCH("k_flag_wait");
+            break;
+        case PH_MAX_POST:
+            k_max_post<<<1, 256, 0, st>>>(P, g, dist_grid(local_cap, 2048), epoch);
+            KD_DLAUNCH("k_max_post");
+            break;
+        case PH_MAX_WAIT:
+            k_max_wait_swap<<<1, 32, 0, st>>>(P, g, cur, epoch);
+            KD_DLAUNCH("k_max_wait_swap");
+            break;
+        case PH_FIX_POST:
+            k_flag_post<<<1, 32, 0, st>>>(P, g, F_FIX, epoch);
+            KD_DLAUNCH("k_flag_post");
+            break;
+        case PH_FIX_WAIT:
+            k_flag_wait<<<1, 32, 0, st>>>(P, g, F_FIX, epoch);
+            KD_DLAUNCH("k_flag_wait");
+            break;
+        default:
+            return fail("kd_dist_phase: unknown phase");
+    }
+    return 0;
+}
+
+static int dist_levels(int world) {
+    int l = 0;
+    while ((1 << l) < world) ++l;
+    return l;
+}
+
+static int local_build(const HostCtx& H, cudaStream_t st) {
+    const DistParams& P = H.P;
+    const int L = dist_levels(P.world);
+    unsigned lo, n;
+    host_seg_range(P.N, L, (unsigned)P.rank, lo, n);
+    unsigned char* base = P.heap[P.rank];
+    Cols buf[2];
+    for (int b = 0; b < 2; ++b) {
+        for (int c = 0; c < kMaxCarry; ++c) buf[b].c[c] = c < P.ncol ? (float*)(base + P.L.col[b][c]) : nullptr;
+        buf[b].idx = (int32_t*)(base + P.L.idx[b]);
+    }
+    BuildScratch sc;
+    sc.keybuf = nullptr;
+    sc.st = (SegState*)(base + P.L.st);
+    sc.ghist = (unsigned*)(base + P.L.ghist);
+    sc.rec = (MaxRec*)(base + P.L.lrec);
+    sc.err = (int*)(base + P.L.lerr);
+    if (cudaMemsetAsync(sc.ghist, 0, (size_t)P.L.max_seg * kDigitBins * 4, st) != cudaSuccess ||
+        cudaMemsetAsync(sc.err, 0, 256, st) != cudaSuccess)
+        return fail("kd_dist_local_build: cudaMemsetAsync failed");
+    OutPtrs out{};
+    out.n = P.world;
+    for (int r = 0; r < P.world; ++r) {
+        out.perm[r] = (int32_t*)(P.heap[r] + P.L.perm);
+        out.tp[r] = H.with_tp ? (float*)(P.heap[r] + P.L.tp) : nullptr;
+    }
+    return build_core(buf, L & 1, (int64_t)n, P.dim, P.ncol, L, lo, out, nullptr, sc, st);
+}
+
+}  // namespace kd
+
+// ------------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------------
+extern "C" {
+
+static int fill_ctx(const kd_dist_ctx* c, kd::HostCtx& H) {
+    if (!c) return kd::fail("kd_dist: null context");
+    if (c->world < 1 || c->world > kd::kMaxWorld || (c->world & (c->world - 1))) return kd::fail("kd_dist: world must be 1, 2, 4 or 8");
+    if (c->rank < 0 || c->rank >= c->world) return kd::fail("kd_dist: bad rank");
+    if (c->dim < 1 || c->dim > kd::kMaxCarry) return kd::fail("kd_dist: the distributed build supports dim <= 4");
+    if (c->n_total < 64ll * c->world || c->n_total >= (1ll << 31))
+        return kd::fail("kd_dist: need 64 * world <= n_total < 2^31");
+    H.P.world = c->world;
+    H.P.rank = c->rank;
+    H.P.dim = c->dim;
+    H.P.ncol = c->dim;
+    H.P.N = (unsigned)c->n_total;
+    H.with_tp = c->with_tree_points != 0;
+    H.P.L = kd::make_layout(c->n_total, c->dim, c->world, H.with_tp);
+    for (int r = 0; r < kd::kMaxWorld; ++r) H.P.heap[r] = r < c->world ? (unsigned char*)c->heap[r] : nullptr;
+    for (int r = 0; r < c->world; ++r)
+        if (!H.P.heap[r]) return kd::fail("kd_dist: missing heap pointer");
+    return 0;
+}
+
+size_t kd_dist_heap_bytes(int64_t n_total, int dim, int world, int with_tree_points) {
+    if (n_total <= 0 || dim <= 0 || dim > kd::kMaxCarry || world < 1 || world > kd::kMaxWorld) return 0;
+    return kd::make_layout(n_total, dim, world, with_tree_points != 0).bytes;
+}
+
+int kd_dist_offsets(int64_t n_total, int dim, int world, int with_tree_points, size_t* perm_off, size_t* tp_off) {
+    if (n_total <= 0 || dim <= 0 || dim > kd::kMaxCarry || world < 1 || world > kd::kMaxWorld)
+        return kd::fail("kd_dist_offsets: bad arguments");
+    kd::DistLayout L = kd::make_layout(n_total, dim, world, with_tree_points != 0);
+    if (perm_off) *perm_off = L.perm;
+    if (tp_off) *tp_off = L.tp;
+    return 0;
+}
+
+int kd_dist_init(const kd_dist_ctx* ctx, const float* local_points, int64_t local_n, int64_t first_row, void* stream) {
+    kd::HostCtx H;
+    if (int rc = fill_ctx(ctx, H)) return rc;
+    if (!local_points || local_n <= 0 || local_n > H.P.L.cap) return kd::fail("kd_dist_init: bad local slice");
+    cudaStream_t st = (cudaStream_t)stream;
+    // control words and flags start at zero once per heap; epochs only grow afterwards
+    kd::reset_launches();
+    kd::k_dist_init<<<(unsigned)((local_n + 255) / 256), 256, 0, st>>>(H.P, local_points, (unsigned)local_n,
+                                                                      (unsigned)first_row);
+    kd::count_launch();
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : kd::fail(std::string("kd_dist_init: ") + cudaGetErrorString(e));
+}
+
+int kd_dist_phase(const kd_dist_ctx* ctx, int level, int phase, int pass, uint64_t serial, void* stream) {
+    kd::HostCtx H;
+    if (int rc = fill_ctx(ctx, H)) return rc;
+    if (level < 0 || level >= kd::dist_levels(H.P.world)) return kd::fail("kd_dist_phase: bad level");
+    return kd::run_phase(H, level, phase, pass, serial, (cudaStream_t)stream);
+}
+
+int kd_dist_local_build(const kd_dist_ctx* ctx, void* stream) {
+    kd::HostCtx H;
+    if (int rc = fill_ctx(ctx, H)) return rc;
+    return kd::local_build(H, (cudaStream_t)stream);
+}
+
+int kd_dist_done(const kd_dist_ctx* ctx, int post, uint64_t serial, void* stream) {
+    kd::HostCtx H;
+    if (int rc = fill_ctx(ctx, H)) return rc;
+    kd::LevelGeo g = kd::make_geo(H.P, 0);  // the whole world is one group
+    const unsigned long long epoch = serial * 64ull + 63ull;
+    if (post) kd::k_flag_post<<<1, 32, 0, (cudaStream_t)stream>>>(H.P, g, kd::F_DONE, epoch);
+    else kd::k_flag_wait<<<1, 32, 0, (cudaStream_t)stream>>>(H.P, g, kd::F_DONE, epoch);
+    kd::count_launch();
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : kd::fail(std::string("kd_dist_done: ") + cudaGetErrorString(e));
+}
+
+// one rank's whole build, in program order (one process per GPU)
+int kd_dist_run(const kd_dist_ctx* ctx, uint64_t serial, void* stream) {
+    kd::HostCtx H;
+    if (int rc = fill_ctx(ctx, H)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int L = kd::dist_levels(H.P.world);
+    for (int level = 0; level < L; ++level) {
+        if (int rc = kd::run_phase(H, level, kd::PH_STATE, 0, serial, st)) return rc;
+        for (int d = 0; d < kd::kNumDigits; ++d) {
+            if (int rc = kd::run_phase(H, level, kd::PH_HIST, d, serial, st)) return rc;
+            if (int rc = kd::run_phase(H, level, kd::PH_SCAN, d, serial, st)) return rc;
+        }
+        for (int ph = kd::PH_CNT_POST; ph < kd::kNumPhases; ++ph)
+            if (int rc = kd::run_phase(H, level, ph, 7, serial, st)) return rc;
+    }
+    if (int rc = kd::local_build(H, st)) return rc;
+    if (int rc = kd_dist_done(ctx, 1, serial, stream)) return rc;
+    return kd_dist_done(ctx, 0, serial, stream);
+}
+
+int kd_dist_status(const kd_dist_ctx* ctx, void* stream) {
+    kd::HostCtx H;
+    if (int rc = fill_ctx(ctx, H)) return rc;
+    int host_err[2] = {0, 0};
+    int* dev_err = (int*)(H.P.heap[H.P.rank] + H.P.L.lerr) + 8;
+    kd::k_dist_read_err<<<1, 1, 0, (cudaStream_t)stream>>>(H.P, dev_err);
+    cudaError_t e = cudaMemcpyAsync(&host_err[0], dev_err, sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(&host_err[1], H.P.heap[H.P.rank] + H.P.L.lerr, sizeof(int), cudaMemcpyDeviceToHost,
+                            (cudaStream_t)stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize((cudaStream_t)stream);
+    if (e != cudaSuccess) return kd::fail(std::string("kd_dist_status: ") + cudaGetErrorString(e));
+    if (host_err[0]) return kd::fail("distributed build failed on the device, code " + std::to_string(host_err[0]));
+    if (host_err[1]) return kd::fail("local phase of the distributed build failed, digit pass " + std::to_string(host_err[1] - 1));
+    return 0;
+}
+
+// ---- symmetric heap runtime (H6): allocation + CUDA IPC handles; exchange of the handles is the caller's
+// job (torch.distributed object collectives), nothing else goes through a collective library ----
+int kd_symm_alloc(size_t bytes, void** ptr, void* handle64) {
+    if (!ptr || !handle64 || bytes == 0) return kd::fail("kd_symm_alloc: bad arguments");
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) return kd::fail(std::string("kd_symm_alloc: cudaMalloc: ") + cudaGetErrorString(e));
+    e = cudaMemset(p, 0, bytes);
+    cudaIpcMemHandle_t h;
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) { cudaFree(p); return kd::fail(std::string("kd_symm_alloc: ") + cudaGetErrorString(e)); }
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    std::memcpy(handle64, &h, 64);
+    *ptr = p;
+    return 0;
+}
+
+int kd_symm_open(const void* handle64, void** ptr) {
+    if (!handle64 || !ptr) return kd::fail("kd_symm_open: bad arguments");
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle64, 64);
+    void* p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) return kd::fail(std::string("kd_symm_open: cudaIpcOpenMemHandle: ") + cudaGetErrorString(e));
+    *ptr = p;
+    return 0;
+}
+
+int kd_symm_close(void* ptr) {
+    cudaError_t e = cudaIpcCloseMemHandle(ptr);
+    return e == cudaSuccess ? 0 : kd::fail(std::string("kd_symm_close: ") + cudaGetErrorString(e));
+}
+
+int kd_symm_free(void* ptr) {
+    cudaError_t e = cudaFree(ptr);
+    return e == cudaSuccess ? 0 : kd::fail(std::string("kd_symm_free: ") + cudaGetErrorString(e));
+}
+
+int kd_symm_memset(void* ptr, size_t bytes, void* stream) {
+    cudaError_t e = cudaMemsetAsync(ptr, 0, bytes, (cudaStream_t)stream);
+    return e == cudaSuccess ? 0 : kd::fail(std::string("kd_symm_memset: ") + cudaGetErrorString(e));
+}
+
+}  // extern "C"

@@ -1,0 +1,37 @@
+"""Distributed global build (csrc/dist_kernels.cu) — W virtual ranks on one GPU run the real kernels in the
+real order; the oracle is the CPU builder (= the reference's sequential tree, see test_host_core.py)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("n,dim", [(100003, 3), (1 << 18, 2), (300000, 3), (70001, 1), (250000, 4)])
+def test_emulated_ranks_build_the_sequential_tree(kd, world, n, dim):
+    from parallel_kd_tree_b200.parallel.dist_build import EmulatedDistBuild
+    pts = kd.ops.generate_uniform(n % 89 + 1, dim, n)
+    ref = kd.ops.build(pts)[0]
+    eb = EmulatedDistBuild(n, dim, world)
+    outs = eb.build(pts)
+    torch.cuda.synchronize()
+    for r, (perm, tp) in enumerate(outs):
+        got = perm.cpu()
+        if not torch.equal(got, ref):
+            bad = (got != ref).nonzero().flatten()
+            pytest.fail(f"rank {r}: {bad.numel()} of {n} slots differ, first {bad[:8].tolist()}")
+        assert torch.equal(tp.cpu(), pts[ref.long()])
+
+
+def test_emulated_ranks_heavy_ties_and_rebuild(kd):
+    from parallel_kd_tree_b200.parallel.dist_build import EmulatedDistBuild
+    g = torch.Generator().manual_seed(3)
+    n, dim, world = 200000, 3, 4
+    eb = EmulatedDistBuild(n, dim, world)
+    for trial in range(2):                      # the second build reuses the heap (flags keep growing epochs)
+        pts = torch.randint(-3, 4, (n, dim), generator=g).float()
+        ref = kd.ops.build(pts)[0]
+        outs = eb.build(pts)
+        torch.cuda.synchronize()
+        for perm, _ in outs:
+            assert torch.equal(perm.cpu(), ref)
