@@ -142,7 +142,7 @@ def run_ours(args) -> dict:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
         from parallel_kd_tree_b200.parallel import bench_distributed
-        return bench_distributed.run(args, kd, dist, rank, world, dev)
+        return bench_distributed.run(args, kd, dist, rank, world, dev, ClockSampler, BASELINE_POINTS_PER_S)
 
     gen = kd.ops.generate_clustered if args.dist == "clustered" else kd.ops.generate_uniform
     t0 = time.time()

@@ -113,6 +113,13 @@ int kd_dist_done(const kd_dist_ctx* ctx, int post, uint64_t serial, void* stream
 /* synchronises the stream; non-zero if a device-side check or a peer wait failed */
 int kd_dist_status(const kd_dist_ctx* ctx, void* stream);
 
+/* ---- forest mode (kdtree_mpi.cpp:204-253): per-query minimum of the ranks' distances, folded into rank 0's
+ * buffer with system-scope atomicMin over peer memory (replaces MPI_Reduce(MPI_MIN), kdtree_mpi.cpp:252-253).
+ * Buffers are kd_forest_buf_bytes(nq) bytes from kd_symm_alloc; `epoch` must grow with every call. ---- */
+size_t kd_forest_buf_bytes(int nq);
+int kd_forest_min_reduce(void* root_buf, void* my_buf, int rank, int world, const float* dist, int nq, float* out,
+                         uint64_t epoch, int* err, void* stream);
+
 /* ---- symmetric-heap runtime: allocation and CUDA IPC mapping (handle exchange is the caller's job) ---- */
 int kd_symm_alloc(size_t bytes, void** ptr, void* handle64);
 int kd_symm_open(const void* handle64, void** ptr);

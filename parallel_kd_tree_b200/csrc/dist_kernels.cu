@@ -870,3 +870,61 @@ int kd_symm_memset(void* ptr, size_t bytes, void* stream) {
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// K8: forest min-reduce (the reference's MPI_Reduce(MPI_MIN) of the per-rank query distances,
+// kdtree_mpi.cpp:252-253) as one kernel per rank over peer memory: every rank folds its distances into
+// rank 0's buffer with system-scope atomicMin (distances are >= 0, so their float bits order like
+// unsigned integers) and raises a flag there; rank 0 waits for all flags and decodes.
+// Buffer layout per rank (a small symmetric allocation): u64 ready[8] | u64 done[8] | u32 val[nq].
+// ------------------------------------------------------------------------------------------------
+namespace kd {
+struct ForestBuf {
+    unsigned long long ready[kMaxWorld];
+    unsigned long long done[kMaxWorld];
+    unsigned val[1];
+};
+
+__global__ void k_forest_min(ForestBuf* root, ForestBuf* mine, int rank, int world, const float* __restrict__ dist,
+                             int nq, float* __restrict__ out, unsigned long long epoch, int* err) {
+    const int tid = threadIdx.x;
+    if (rank == 0) {
+        for (int q = tid; q < nq; q += blockDim.x) root->val[q] = 0xffffffffu;
+        __threadfence_system();
+        __syncthreads();
+        // tell every rank (through its own buffer) that the accumulator is initialised
+        // (peers poll their local `ready[0]`, which rank 0 cannot reach here, so they poll root->ready[rank])
+        if (tid < world) st_release_sys(&root->ready[tid], epoch);
+    } else {
+        if (tid == 0 && !wait_flag(&root->ready[rank], epoch)) atomicExch(err, 500);
+        __syncthreads();
+    }
+    for (int q = tid; q < nq; q += blockDim.x) atomicMin_system(&root->val[q], __float_as_uint(dist[q]));
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) st_release_sys(&root->done[rank], epoch);
+    if (rank == 0) {
+        if (tid < world && !wait_flag(&root->done[tid], epoch)) atomicExch(err, 501);
+        __syncthreads();
+        for (int q = tid; q < nq; q += blockDim.x) out[q] = __uint_as_float(__ldcg(&root->val[q]));
+    }
+    (void)mine;
+}
+}  // namespace kd
+
+extern "C" {
+size_t kd_forest_buf_bytes(int nq) { return sizeof(kd::ForestBuf) + (size_t)(nq > 0 ? nq : 1) * 4 + 64; }
+
+/* dist: this rank's nq distances (device); out: rank 0 receives the per-query minimum (device, may be NULL
+ * elsewhere); root_buf: rank 0's buffer as addressable from this rank; err: device int. */
+int kd_forest_min_reduce(void* root_buf, void* my_buf, int rank, int world, const float* dist, int nq, float* out,
+                         uint64_t epoch, int* err, void* stream) {
+    if (!root_buf || !dist || nq <= 0 || world < 1 || world > kd::kMaxWorld || rank < 0 || rank >= world || !err ||
+        (rank == 0 && !out))
+        return kd::fail("kd_forest_min_reduce: bad arguments");
+    kd::k_forest_min<<<1, 256, 0, (cudaStream_t)stream>>>((kd::ForestBuf*)root_buf, (kd::ForestBuf*)my_buf, rank, world,
+                                                         dist, nq, out, epoch, err);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : kd::fail(std::string("kd_forest_min_reduce: ") + cudaGetErrorString(e));
+}
+}

@@ -1,0 +1,98 @@
+"""Multi-GPU arm of bench.py: the distributed global build (one process per GPU, peer memory)."""
+from __future__ import annotations
+
+import os
+import time
+
+import torch
+
+from .dist_build import IpcDistBuild
+
+
+def run(args, kd, dist, rank, world, dev, sampler_cls, baseline_pps):
+    n, dim = 1 << args.log2n, args.dim
+    first, local = kd.models.slice_bounds(n, world, rank)
+    t0 = time.time()
+    # every rank regenerates only its slice of the stream, like kdtree_mpi.cpp:19-41
+    if args.dist == "clustered":
+        host_local = kd.ops.generate_clustered(args.seed, dim, n, pin_memory=False)[first:first + local].contiguous().pin_memory()
+    else:
+        host_local = kd.ops.generate_uniform(args.seed, dim, local, first, pin_memory=True)
+    gen_s = time.time() - t0
+    local_pts = host_local.to(dev, non_blocking=True)
+    db = IpcDistBuild(n, dim, with_tree_points=True)
+    host_perm = torch.empty(local, dtype=torch.int32, pin_memory=True)
+    torch.cuda.synchronize()
+
+    def step():
+        db.load(local_pts)      # SoA transpose of the local slice into the symmetric heap (k_init's counterpart)
+        db.run()
+
+    for _ in range(args.warmup):
+        step()
+    db.status()                 # surfaces device-side failures / peer time-outs (untimed)
+    launches_per_step = int(kd.lib().kd_last_launch_count())
+    dist.barrier()
+    torch.cuda.synchronize()
+
+    sampler = sampler_cls(int(os.environ.get("LOCAL_RANK", "0")))
+    if rank == 0:
+        sampler.start()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    dist.barrier()
+    torch.cuda.synchronize()
+    for a, b in evs:
+        a.record()
+        step()
+        b.record()
+    torch.cuda.synchronize()
+    dist.barrier()
+    total_ms = torch.tensor([sum(a.elapsed_time(b) for a, b in evs)], device=dev)
+    dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)     # max over ranks of the device time
+    clocks = sampler.stop() if rank == 0 else None
+    ms_per_step = float(total_ms.item()) / args.steps
+    db.status()
+
+    # end to end: pinned host slice -> device -> distributed build -> this rank's share of perm back on the host
+    def e2e_step():
+        local_pts.copy_(host_local, non_blocking=True)
+        step()
+        host_perm.copy_(db.perm[first:first + local], non_blocking=True)
+
+    e2e_step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+        torch.cuda.synchronize()
+    e2e = torch.tensor([(time.perf_counter() - t0) / args.steps], device=dev)
+    dist.all_reduce(e2e, op=dist.ReduceOp.MAX)
+    e2e_s = float(e2e.item())
+
+    # cheap sanity check of the replicated result: every rank must hold the same permutation
+    chk = torch.stack([db.perm.long().sum(), (db.perm.long() * torch.arange(n, device=dev)).sum() % 1000003])
+    lo, hi = chk.clone(), chk.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    consistent = bool(torch.equal(lo, hi)) and int(chk[0].item()) == n * (n - 1) // 2
+    value = n / (ms_per_step * 1e-3)
+    out = {
+        "metric": "kd-tree build points/sec", "value": value, "unit": "points/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": value / baseline_pps, "dtype": "fp32", "data": "synthetic",
+        "config": {"model": "kd-tree build (reference rule, ONE global tree, perm + tree-ordered coords replicated "
+                            "on every GPU)",
+                   "n_points": n, "dim": dim, "distribution": args.dist, "seed": args.seed, "global_batch": n,
+                   "parallelism": f"distributed-global-tree x{world} (peer-memory select / partition / all-gather, "
+                                  "no NCCL on the data path)",
+                   "l2": "inputs and working set exceed the 126 MB L2; no flush needed",
+                   "baseline": "BASELINE.md row 15: reference forest W=8 build, 4.2e5 points/s",
+                   "replicas_consistent": consistent, "host_generate_s": round(gen_s, 2)},
+        "clocks": clocks,
+        "e2e": {"value": n / e2e_s, "unit": "points/s", "ms_per_step": e2e_s * 1e3,
+                "h2d_bytes_per_step": host_local.numel() * 4 * world, "d2h_bytes_per_step": n * 4},
+        "gpu_launches": int(launches_per_step * args.steps),
+    }
+    db.close()
+    return out

@@ -85,3 +85,20 @@ def test_default_problem_stdin_seed_golden_lines():
     assert r.returncode == 0
     assert r.stdout == GOLDEN_SEED1
     assert r.stderr.startswith("Specify seed \tUsing seed 1\n")
+
+
+@pytest.mark.slow
+def test_mpi_program_under_torchrun_gloo_two_ranks(oracle):
+    # one process per rank like `mpirun -np 2 ./mpi`; CPU ranks reduce with the gloo collective
+    import socket
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), "-m", "parallel_kd_tree_b200",
+                        "mpi", "--device", "cpu", "3", "3", "4001"], capture_output=True, text=True, cwd=ROOT,
+                       timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = [ln for ln in r.stdout.splitlines() if ln.startswith(("READY", "ID:", "DONE"))]
+    assert out[0] == "READY" and out[-1] == "DONE"
+    assert "\n".join(out[1:11]) + "\n" == oracle.forest_lines(3, 3, 4001, 10, 2)
