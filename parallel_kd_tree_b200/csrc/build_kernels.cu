@@ -214,6 +214,9 @@ __global__ void __launch_bounds__(BLOCK) k_partition(Cols src, Cols dst, const f
     const unsigned long long want = prefix >> shift;
     unsigned long long best = 0ull;
     unsigned bestpos = 0, bestvalid = 0;
+    bool has_node = false;
+    int node_id = 0;
+    float node_val[NCOL > 0 ? NCOL : 1];
 
     if (j == (unsigned)cps - 1 && tid == 0) {  // the pinned element keeps its slot: last of the right range
         unsigned p = lo + n - 1;
@@ -277,16 +280,11 @@ __global__ void __launch_bounds__(BLOCK) k_partition(Cols src, Cols dst, const f
 #pragma unroll
         for (int k = 0; k < IPT; ++k) {
             if (side[k] == 2) continue;
-            if (side[k] == 0) {
-                // the node of this range: final slot lo + n/2 (kdtree_sequential.cpp:51,65)
-                // (written to every replica of the tree arrays: the all-gather is part of the store)
-                for (int r = 0; r < out.n; ++r) {
-                    out.perm[r][out_lo + lo + m] = id[k];
-                    if (out.tp[r]) {
+            if (side[k] == 0) {  // the node of this range: remembered, stored once after the sweep
+                node_id = id[k];
+                has_node = true;
 #pragma unroll
-                        for (int c = 0; c < NCOL; ++c) out.tp[r][(size_t)(out_lo + lo + m) * dim + c] = val[k][c];
-                    }
-                }
+                for (int c = 0; c < NCOL; ++c) node_val[c] = val[k][c];
                 continue;
             }
             unsigned p = (side[k] == -1 ? baseL : baseR) + rk[k];
@@ -296,6 +294,17 @@ __global__ void __launch_bounds__(BLOCK) k_partition(Cols src, Cols dst, const f
             if (side[k] == -1) {
                 unsigned long long c = composite(ordered_key(kf[k]), (unsigned)id[k]);
                 if (!bestvalid || c > best) { best = c; bestpos = p; bestvalid = 1; }
+            }
+        }
+    }
+    if (has_node) {
+        // the node's final slot is lo + n/2 (kdtree_sequential.cpp:51,65) in every replica of the tree arrays
+        // (the all-gather of a distributed build is part of this store)
+        for (int r = 0; r < out.n; ++r) {
+            out.perm[r][out_lo + lo + m] = node_id;
+            if (out.tp[r]) {
+#pragma unroll
+                for (int c = 0; c < NCOL; ++c) out.tp[r][(size_t)(out_lo + lo + m) * dim + c] = node_val[c];
             }
         }
     }
@@ -347,6 +356,179 @@ __global__ void __launch_bounds__(256) k_fixup(Cols dst, int ncol, const MaxRec*
         int32_t a = dst.idx[bestpos], b = dst.idx[last];
         dst.idx[bestpos] = b;
         dst.idx[last] = a;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K2+K3 for medium ranges (kFinishEff < n <= kMediumMax): ONE CTA owns the range for the whole
+// level.  The split-axis keys are staged in shared memory once, every digit pass of the select
+// runs on them (shared-memory histogram, no global atomics, no global histogram), then a single
+// sweep moves the points: the node to its final slot, the left range's maximum straight to the left
+// range's last slot (found before the sweep, so no fix-up kernel), everything else to slots claimed
+// with warp-aggregated shared-memory cursors.  HBM traffic per level: keys once + points once in,
+// points once out.
+// ------------------------------------------------------------------------------------------
+template <int NCOL>
+__global__ void __launch_bounds__(512) k_medium(Cols src, Cols dst, const float* __restrict__ keys, int axis,
+                                                OutPtrs out, unsigned out_lo, int dim, unsigned N, int level,
+                                                unsigned cap, int* err) {
+    extern __shared__ __align__(16) unsigned char msm[];
+    unsigned* skey = reinterpret_cast<unsigned*>(msm);   // [cap] ordered keys of the unpinned elements
+    unsigned* hist = skey + cap;                         // [kDigitBins]
+    __shared__ unsigned s_w[16];
+    __shared__ unsigned long long s_prefix, s_best;
+    __shared__ unsigned s_rank, s_cnt, s_done, s_cur[2], s_kmax, s_cum;
+    __shared__ int s_shift, s_bin;
+    const unsigned tid = threadIdx.x, B = blockDim.x, lane = tid & 31, wid = tid >> 5;
+    unsigned lo, n;
+    seg_range(N, level, blockIdx.x, lo, n);
+    const unsigned m = n >> 1, free_n = n - 1;
+    const float* __restrict__ kcol = NCOL > 0 ? src.c[axis] : keys;
+    for (unsigned i = tid; i < free_n; i += B) skey[i] = ordered_key(kcol[lo + i]);
+    if (tid == 0) { s_prefix = 0ull; s_rank = m; s_done = 0; s_shift = 64; s_cur[0] = s_cur[1] = 0; s_kmax = 0; s_best = 0ull; }
+    __syncthreads();
+    // ---- select: rank m of the free_n composites (key, index) ----
+    for (int d = 0; d < kNumDigits; ++d) {
+        for (unsigned t = tid; t < (unsigned)kDigitBins; t += B) hist[t] = 0;
+        __syncthreads();
+        if (s_done) break;
+        const unsigned long long prefix = s_prefix;
+        const int dsh = digit_shift(d);
+        const unsigned mask = (1u << digit_bits(d)) - 1u;
+        const unsigned iters = (free_n + B - 1) / B;
+        for (unsigned it = 0; it < iters; ++it) {
+            const unsigned i = it * B + tid;
+            bool valid = i < free_n;
+            const unsigned key = valid ? skey[i] : 0u;
+            unsigned digit;
+            if (d < 3) {
+                if (d > 0) valid = valid && ((key >> (digit_shift(d - 1) - 32)) == (unsigned)(prefix >> digit_shift(d - 1)));
+                digit = (key >> (dsh - 32)) & mask;
+            } else {
+                valid = valid && key == (unsigned)(prefix >> 32);
+                const unsigned id = valid ? (unsigned)src.idx[lo + i] : 0u;
+                if (d > 3) valid = valid && ((id >> digit_shift(d - 1)) == ((unsigned)(prefix & 0xffffffffull) >> digit_shift(d - 1)));
+                digit = (id >> dsh) & mask;
+            }
+            warp_hist_add(hist, digit, valid);
+        }
+        __syncthreads();
+        // locate the bin of the wanted rank: each thread owns kDigitBins / B consecutive bins
+        const unsigned per = (unsigned)kDigitBins / B;
+        unsigned sum = 0;
+        for (unsigned k = 0; k < per; ++k) sum += hist[tid * per + k];
+        unsigned inc = sum;
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= (unsigned)o) inc += t;
+        }
+        if (lane == 31) s_w[wid] = inc;
+        if (tid == 0) s_bin = -1;
+        __syncthreads();
+        unsigned base = 0;
+        for (unsigned k = 0; k < wid; ++k) base += s_w[k];
+        unsigned c = base + inc - sum;
+        const unsigned r = s_rank;
+        for (unsigned k = 0; k < per; ++k) {
+            const unsigned v = hist[tid * per + k];
+            if (r >= c && r < c + v) { s_bin = (int)(tid * per + k); s_cnt = v; s_cum = c; }
+            c += v;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            if (s_bin < 0) { atomicExch(err, 11 + d); s_done = 1; }
+            else {
+                s_prefix = prefix | ((unsigned long long)(unsigned)s_bin << dsh);
+                s_rank = r - s_cum;
+                s_shift = dsh;
+                if (s_cnt == 1u || d == kNumDigits - 1) s_done = 1;
+            }
+        }
+        __syncthreads();
+    }
+    __syncthreads();
+    const int shift = s_shift;
+    const unsigned long long want = s_prefix >> shift;
+    const unsigned wantkey_hi = shift >= 32 ? 0u : (unsigned)(s_prefix >> 32);
+    // side of element i: -1 left, 0 node, 1 right.  The index is read only when the key alone cannot decide.
+    auto classify = [&](unsigned i, unsigned key, unsigned& id, bool& have_id) -> int {
+        have_id = false;
+        id = 0;
+        if (shift < 32 && key == wantkey_hi) { id = (unsigned)src.idx[lo + i]; have_id = true; }
+        const unsigned long long c = composite(key, id) >> shift;
+        return c < want ? -1 : (c > want ? 1 : 0);
+    };
+    // ---- the left range's maximum (key first, index among equal keys) ----
+    unsigned kmax = 0;
+    bool any_left = false;
+    for (unsigned i = tid; i < free_n; i += B) {
+        unsigned id; bool have;
+        const unsigned key = skey[i];
+        if (classify(i, key, id, have) == -1) { kmax = any_left ? max(kmax, key) : key; any_left = true; }
+    }
+    if (any_left) atomicMax(&s_kmax, kmax);
+    __syncthreads();
+    kmax = s_kmax;
+    for (unsigned i = tid; i < free_n; i += B) {
+        const unsigned key = skey[i];
+        if (key != kmax) continue;
+        unsigned id; bool have;
+        if (classify(i, key, id, have) != -1) continue;
+        if (!have) id = (unsigned)src.idx[lo + i];
+        atomicMax(&s_best, ((unsigned long long)id << 32) | i);
+    }
+    __syncthreads();
+    const unsigned pmax = (unsigned)(s_best & 0xffffffffull);  // position (inside the range) of the left maximum
+    // ---- move the points ----
+    if (tid == 0) {  // the pinned element keeps its slot: last of the right range
+        const unsigned p = lo + n - 1;
+#pragma unroll
+        for (int c = 0; c < NCOL; ++c) dst.c[c][p] = src.c[c][p];
+        dst.idx[p] = src.idx[p];
+    }
+    const unsigned iters = (free_n + B - 1) / B;
+    for (unsigned it = 0; it < iters; ++it) {
+        const unsigned i = it * B + tid;
+        const bool valid = i < free_n;
+        float val[NCOL > 0 ? NCOL : 1];
+        int id = 0;
+        int side = 2;
+        if (valid) {
+            id = src.idx[lo + i];
+#pragma unroll
+            for (int c = 0; c < NCOL; ++c) val[c] = src.c[c][lo + i];
+            const unsigned long long c = composite(skey[i], (unsigned)id) >> shift;
+            side = c < want ? -1 : (c > want ? 1 : 0);
+            if (i == pmax) side = -2;  // the left maximum: goes to the left range's last slot
+        }
+        const unsigned bl = __ballot_sync(0xffffffffu, side == -1);
+        const unsigned br = __ballot_sync(0xffffffffu, side == 1);
+        unsigned wl = 0, wr = 0;
+        if (lane == 0) {
+            if (bl) wl = atomicAdd(&s_cur[0], __popc(bl));
+            if (br) wr = atomicAdd(&s_cur[1], __popc(br));
+        }
+        wl = __shfl_sync(0xffffffffu, wl, 0);
+        wr = __shfl_sync(0xffffffffu, wr, 0);
+        const unsigned lt = (1u << lane) - 1u;
+        if (side == 2) continue;
+        if (side == 0) {  // the node: final slot lo + n/2 in every replica of the tree arrays
+            for (int r = 0; r < out.n; ++r) {
+                out.perm[r][out_lo + lo + m] = id;
+                if (out.tp[r]) {
+#pragma unroll
+                    for (int c = 0; c < NCOL; ++c) out.tp[r][(size_t)(out_lo + lo + m) * dim + c] = val[c];
+                }
+            }
+            continue;
+        }
+        unsigned p;
+        if (side == -2) p = lo + m - 1;
+        else if (side == -1) p = lo + wl + __popc(bl & lt);
+        else p = lo + m + 1 + wr + __popc(br & lt);
+#pragma unroll
+        for (int c = 0; c < NCOL; ++c) dst.c[c][p] = val[c];
+        dst.idx[p] = id;
     }
 }
 
@@ -405,7 +587,7 @@ __device__ __forceinline__ void fin_reg_step(unsigned (&key)[8], unsigned (&slot
 
 __global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, const float* __restrict__ pts,
                                                             int dim, unsigned N, int level, int depth0,
-                                                            OutPtrs out, unsigned out_lo) {
+                                                            OutPtrs out, unsigned out_lo, int skip) {
     extern __shared__ __align__(16) unsigned char smem[];
     constexpr int T = kFinishT;
     unsigned lo, n;
@@ -425,8 +607,26 @@ __global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, 
     }
     if (tid == 0) stab[0] = n;  // sub-range 0 of sub-level 0: lo = 0, size n
     __syncthreads();
+    // The first `skip` sub-levels of this range were already split by the select/partition kernels: only
+    // walk the table down, and mark their node slots (already final in the tree arrays) as not ours.
+    for (int j = 0; j < skip; ++j) {
+        const unsigned nsub = 1u << j;
+        unsigned ent[2];
+        int cnt = 0;
+        for (unsigned q = tid; q < nsub; q += kFinishBlock) ent[cnt++] = stab[q];
+        __syncthreads();
+        cnt = 0;
+        for (unsigned q = tid; q < nsub; q += kFinishBlock) {
+            const unsigned tb = ent[cnt++];
+            const unsigned sn = tb & 0xffffu, slo = tb >> 16, m = sn >> 1;
+            if (sn) sord[slo + m] = (unsigned short)kInfSlot;
+            stab[2 * q] = (slo << 16) | m;
+            stab[2 * q + 1] = sn ? (((slo + m + 1u) << 16) | (sn - m - 1u)) : (slo << 16);
+        }
+        __syncthreads();
+    }
     const unsigned vbase = tid * 8u;
-    for (int j = 0; (n >> j) >= 3u; ++j) {
+    for (int j = skip; (n >> j) >= 3u; ++j) {
         const unsigned nsub = 1u << j;
         const int axis = (depth0 + level + j) % dim;
         const unsigned maxsort = (n >> j) - 1u;  // the left-most sub-range is the largest
@@ -504,6 +704,7 @@ __global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, 
         float* __restrict__ tree_pts = out.tp[r];
         for (unsigned p = tid; p < n; p += kFinishBlock) {
             unsigned slot = sord[p];
+            if (slot == kInfSlot) continue;  // a node placed by an earlier level
             perm[out_lo + lo + p] = sidx[slot];
             if (tree_pts && ncol)
                 for (int c = 0; c < ncol; ++c) tree_pts[(size_t)(out_lo + lo + p) * dim + c] = scol[c * T + slot];
@@ -531,11 +732,12 @@ BuildPlan make_plan(int64_t n, int dim) {
     p.n = n;
     p.dim = dim;
     p.ncol = dim <= kMaxCarry ? dim : 0;
-    // level at which every range fits the finisher (the left-most range is the largest: n >> level)
+    // levels handled with several CTAs per range and a global histogram: while the largest range
+    // (the left-most one, n >> level) exceeds kMediumMax
     int lv = 0;
-    while ((n >> lv) > kFinishT) ++lv;
+    while ((n >> lv) > kMediumMax) ++lv;
     p.finish_level = lv;
-    p.max_seg = lv == 0 ? 1 : (1ll << (lv - 1));  // ranges of the deepest select/partition level
+    p.max_seg = lv == 0 ? 1 : (1ll << (lv - 1));  // ranges of the deepest such level
     p.max_rec = p.max_seg + kTargetCtas;
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
@@ -578,15 +780,53 @@ int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, u
         if (e != cudaSuccess) return fail(std::string("kd build: cudaFuncSetAttribute: ") + cudaGetErrorString(e));
     }
     const unsigned N = (unsigned)n;
+    // Level schedule: select/partition with several CTAs per range while ranges are large, one CTA per
+    // range (k_medium) while they exceed kFinishEff, then the shared-memory finisher.  A finisher CTA
+    // always works on a window of up to kFinishT slots, i.e. on the ancestor `skip` levels up.
     int finish_level = 0;
-    while ((n >> finish_level) > kFinishT) ++finish_level;
+    while ((n >> finish_level) > kFinishEff) ++finish_level;
+    int skip = 0;
+    while (skip < finish_level && (n >> (finish_level - skip - 1)) <= kFinishT) ++skip;
+    {
+        cudaError_t e = cudaSuccess;
+#define KD_MED_ATTR(NC) if (e == cudaSuccess) e = cudaFuncSetAttribute(k_medium<NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)medium_smem_bytes())
+        KD_MED_ATTR(0); KD_MED_ATTR(1); KD_MED_ATTR(2); KD_MED_ATTR(3); KD_MED_ATTR(4);
+#undef KD_MED_ATTR
+        if (e != cudaSuccess) return fail(std::string("kd build: cudaFuncSetAttribute: ") + cudaGetErrorString(e));
+    }
     for (int level = 0;; ++level) {
         const int64_t nseg = 1ll << level;
         if (level == finish_level) {
-            k_finish<<<(unsigned)nseg, kFinishBlock, fin_smem, stream>>>(buf[cur], ncol, points, dim, N, level, depth0,
-                                                                        out, out_lo);
+            k_finish<<<(unsigned)(nseg >> skip), kFinishBlock, fin_smem, stream>>>(buf[cur], ncol, points, dim, N,
+                                                                                  level - skip, depth0, out, out_lo,
+                                                                                  skip);
             KD_LAUNCH_CHECK("k_finish");
             break;
+        }
+        if ((n >> level) <= kMediumMax) {
+            const int axis = (depth0 + level) % dim;
+            const float* keys = nullptr;
+            if (!ncol) {
+                k_gather_keys<<<(unsigned)nseg, 256, 0, stream>>>(points, dim, axis, buf[cur].idx, sc.keybuf, N, level, 1);
+                KD_LAUNCH_CHECK("k_gather_keys");
+                keys = sc.keybuf;
+            }
+            const int64_t seg_n = n >> level;
+            const int block = seg_n > 4096 ? 512 : (seg_n > 1024 ? 256 : 128);
+            const unsigned cap = (unsigned)((seg_n + 31) & ~31ll);   // shared memory sized to the level's ranges
+            const size_t msmem = (size_t)cap * 4 + (size_t)kDigitBins * 4;
+#define KD_MED(NC) k_medium<NC><<<(unsigned)nseg, block, msmem, stream>>>(buf[cur], buf[cur ^ 1], keys, axis, out, out_lo, dim, N, level, cap, sc.err)
+            switch (ncol) {
+                case 0: KD_MED(0); break;
+                case 1: KD_MED(1); break;
+                case 2: KD_MED(2); break;
+                case 3: KD_MED(3); break;
+                default: KD_MED(4); break;
+            }
+#undef KD_MED
+            KD_LAUNCH_CHECK("k_medium");
+            cur ^= 1;
+            continue;
         }
         const int64_t seg_n = n >> level;
         const int axis = (depth0 + level) % dim;

@@ -8,6 +8,8 @@ namespace kd {
 constexpr int kMaxCarry = 4;      // dim <= kMaxCarry: coordinates travel with the points (SoA columns);
                                   // larger dim: only indices move and keys are gathered per level
 constexpr int kFinishT = 4096;    // ranges of at most this many points are finished in shared memory
+constexpr int kFinishEff = 512;     // select/partition levels go on until ranges have at most this many points
+constexpr int kMediumMax = 16384;   // ranges up to this size are handled by one CTA per level (k_medium)
 constexpr int kTargetCtas = 148 * 16;
 
 struct SegState {
@@ -72,6 +74,8 @@ int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, u
 void count_launch();
 void reset_launches();
 #endif
+
+inline size_t medium_smem_bytes() { return (size_t)kMediumMax * 4 + (size_t)2048 * 4; }
 
 inline size_t finish_smem_bytes(int ncol) {
     // scol[ncol][T] f32, sidx[T] i32, xkey[T] u32, stab[T/2] u32, sord[T] u16, xslot[T] u16

@@ -81,7 +81,7 @@ static DistLayout make_layout(int64_t n_total, int dim, int world, bool with_tp)
     L.perm = take((size_t)n_total * 4);
     L.tp = with_tp ? take((size_t)n_total * dim * 4) : 0;
     int lv = 0;
-    while ((L.cap >> lv) > kFinishT) ++lv;
+    while ((L.cap >> lv) > kMediumMax) ++lv;
     L.max_seg = lv == 0 ? 1 : (1ll << (lv - 1));
     L.max_rec = L.max_seg + kTargetCtas;
     L.st = take((size_t)L.max_seg * sizeof(SegState));
@@ -387,6 +387,9 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
     const unsigned b = min(blockIdx.x * chunk, free_n), e = min(b + chunk, free_n);
     unsigned long long best = 0ull;
     unsigned bestpos = 0, bestvalid = 0;
+    bool has_node = false;
+    int node_id = 0;
+    float node_val[NCOL];
 
     if (last_member && blockIdx.x == gridDim.x - 1 && tid == 0) {
         // the range's pinned element: last element of the right child range, i.e. of the group's last member
@@ -450,16 +453,11 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
 #pragma unroll
         for (int k = 0; k < IPT; ++k) {
             if (side[k] == 2) continue;
-            if (side[k] == 0) {
-                // the node of this range: slot lo + n/2 of every GPU's tree arrays
-                for (int r = 0; r < P.world; ++r) {
-                    reinterpret_cast<int32_t*>(P.heap[r] + P.L.perm)[g.lo + m] = id[k];
-                    if (with_tp) {
-                        float* tp = reinterpret_cast<float*>(P.heap[r] + P.L.tp);
+            if (side[k] == 0) {  // the node of this range: remembered, stored once after the sweep
+                node_id = id[k];
+                has_node = true;
 #pragma unroll
-                        for (int c = 0; c < NCOL; ++c) tp[(size_t)(g.lo + m) * P.dim + c] = val[k][c];
-                    }
-                }
+                for (int c = 0; c < NCOL; ++c) node_val[c] = val[k][c];
                 continue;
             }
             const bool left = side[k] == -1;
@@ -473,6 +471,17 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
             if (left) {
                 unsigned long long c = composite(key[k], (unsigned)id[k]);
                 if (!bestvalid || c > best) { best = c; bestpos = o; bestvalid = 1; }
+            }
+        }
+    }
+    if (has_node) {
+        // the node of this range: slot lo + n/2 of every GPU's tree arrays
+        for (int r = 0; r < P.world; ++r) {
+            reinterpret_cast<int32_t*>(P.heap[r] + P.L.perm)[g.lo + m] = node_id;
+            if (with_tp) {
+                float* tp = reinterpret_cast<float*>(P.heap[r] + P.L.tp);
+#pragma unroll
+                for (int c = 0; c < NCOL; ++c) tp[(size_t)(g.lo + m) * P.dim + c] = node_val[c];
             }
         }
     }
