@@ -368,13 +368,20 @@ __global__ void __launch_bounds__(256) k_fixup(Cols dst, int ncol, const MaxRec*
 // with warp-aggregated shared-memory cursors.  HBM traffic per level: keys once + points once in,
 // points once out.
 // ------------------------------------------------------------------------------------------
-template <int NCOL>
-__global__ void __launch_bounds__(512) k_medium(Cols src, Cols dst, const float* __restrict__ keys, int axis,
+template <int NCOL, int DBITS>
+__global__ void __launch_bounds__(512, 3) k_medium(Cols src, Cols dst, const float* __restrict__ keys, int axis,
                                                 OutPtrs out, unsigned out_lo, int dim, unsigned N, int level,
                                                 unsigned cap, int* err) {
+    // digit schedule over the 64-bit composite: 11/11/10 + 11/11/10 bits (as in k_hist) for the larger
+    // ranges, 8 x 8 bits for the small ones (a 256-bin histogram is cheaper to clear and scan than the
+    // few extra passes over keys that already sit in shared memory)
+    constexpr int kBins = 1 << DBITS;
+    constexpr int kPasses = DBITS == 8 ? 8 : kNumDigits;
+    auto dshift = [](int d) { return DBITS == 8 ? 56 - 8 * d : digit_shift(d); };
+    auto dbits = [](int d) { return DBITS == 8 ? 8 : digit_bits(d); };
     extern __shared__ __align__(16) unsigned char msm[];
     unsigned* skey = reinterpret_cast<unsigned*>(msm);   // [cap] ordered keys of the unpinned elements
-    unsigned* hist = skey + cap;                         // [kDigitBins]
+    unsigned* hist = skey + cap;                         // [kBins]
     __shared__ unsigned s_w[16];
     __shared__ unsigned long long s_prefix, s_best;
     __shared__ unsigned s_rank, s_cnt, s_done, s_cur[2], s_kmax, s_cum;
@@ -384,39 +391,48 @@ __global__ void __launch_bounds__(512) k_medium(Cols src, Cols dst, const float*
     seg_range(N, level, blockIdx.x, lo, n);
     const unsigned m = n >> 1, free_n = n - 1;
     const float* __restrict__ kcol = NCOL > 0 ? src.c[axis] : keys;
-    for (unsigned i = tid; i < free_n; i += B) skey[i] = ordered_key(kcol[lo + i]);
+    for (unsigned i0 = tid; i0 < free_n; i0 += 4 * B) {  // four loads in flight per thread
+        float f[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) f[u] = (i0 + u * B) < free_n ? kcol[lo + i0 + u * B] : 0.f;
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if ((i0 + u * B) < free_n) skey[i0 + u * B] = ordered_key(f[u]);
+    }
     if (tid == 0) { s_prefix = 0ull; s_rank = m; s_done = 0; s_shift = 64; s_cur[0] = s_cur[1] = 0; s_kmax = 0; s_best = 0ull; }
     __syncthreads();
+    const unsigned iters = (free_n + B - 1) / B;
     // ---- select: rank m of the free_n composites (key, index) ----
-    for (int d = 0; d < kNumDigits; ++d) {
-        for (unsigned t = tid; t < (unsigned)kDigitBins; t += B) hist[t] = 0;
+    for (int d = 0; d < kPasses; ++d) {
+        for (unsigned t = tid; t < (unsigned)kBins; t += B) hist[t] = 0;
         __syncthreads();
         if (s_done) break;
         const unsigned long long prefix = s_prefix;
-        const int dsh = digit_shift(d);
-        const unsigned mask = (1u << digit_bits(d)) - 1u;
-        const unsigned iters = (free_n + B - 1) / B;
+        const int dsh = dshift(d), psh = d ? dshift(d - 1) : 64;
+        const unsigned mask = (1u << dbits(d)) - 1u;
         for (unsigned it = 0; it < iters; ++it) {
             const unsigned i = it * B + tid;
             bool valid = i < free_n;
             const unsigned key = valid ? skey[i] : 0u;
             unsigned digit;
-            if (d < 3) {
-                if (d > 0) valid = valid && ((key >> (digit_shift(d - 1) - 32)) == (unsigned)(prefix >> digit_shift(d - 1)));
+            if (dsh >= 32) {   // a digit of the key
+                if (d > 0) valid = valid && ((key >> (psh - 32)) == (unsigned)(prefix >> psh));
                 digit = (key >> (dsh - 32)) & mask;
-            } else {
+            } else {           // a digit of the point index, among the elements whose key equals the node's
                 valid = valid && key == (unsigned)(prefix >> 32);
                 const unsigned id = valid ? (unsigned)src.idx[lo + i] : 0u;
-                if (d > 3) valid = valid && ((id >> digit_shift(d - 1)) == ((unsigned)(prefix & 0xffffffffull) >> digit_shift(d - 1)));
+                if (psh < 32) valid = valid && ((id >> psh) == ((unsigned)(prefix & 0xffffffffull) >> psh));
                 digit = (id >> dsh) & mask;
             }
             warp_hist_add(hist, digit, valid);
         }
         __syncthreads();
-        // locate the bin of the wanted rank: each thread owns kDigitBins / B consecutive bins
-        const unsigned per = (unsigned)kDigitBins / B;
+        // locate the bin of the wanted rank: each of the first kBins / per threads owns `per` consecutive bins
+        const unsigned per = (unsigned)kBins >= B ? (unsigned)kBins / B : 1u;
+        const bool owner = tid * per < (unsigned)kBins;
         unsigned sum = 0;
-        for (unsigned k = 0; k < per; ++k) sum += hist[tid * per + k];
+        if (owner)
+            for (unsigned k = 0; k < per; ++k) sum += hist[tid * per + k];
         unsigned inc = sum;
         for (int o = 1; o < 32; o <<= 1) {
             unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
@@ -429,11 +445,12 @@ __global__ void __launch_bounds__(512) k_medium(Cols src, Cols dst, const float*
         for (unsigned k = 0; k < wid; ++k) base += s_w[k];
         unsigned c = base + inc - sum;
         const unsigned r = s_rank;
-        for (unsigned k = 0; k < per; ++k) {
-            const unsigned v = hist[tid * per + k];
-            if (r >= c && r < c + v) { s_bin = (int)(tid * per + k); s_cnt = v; s_cum = c; }
-            c += v;
-        }
+        if (owner)
+            for (unsigned k = 0; k < per; ++k) {
+                const unsigned v = hist[tid * per + k];
+                if (r >= c && r < c + v) { s_bin = (int)(tid * per + k); s_cnt = v; s_cum = c; }
+                c += v;
+            }
         __syncthreads();
         if (tid == 0) {
             if (s_bin < 0) { atomicExch(err, 11 + d); s_done = 1; }
@@ -441,7 +458,7 @@ __global__ void __launch_bounds__(512) k_medium(Cols src, Cols dst, const float*
                 s_prefix = prefix | ((unsigned long long)(unsigned)s_bin << dsh);
                 s_rank = r - s_cum;
                 s_shift = dsh;
-                if (s_cnt == 1u || d == kNumDigits - 1) s_done = 1;
+                if (s_cnt == 1u || d == kPasses - 1) s_done = 1;
             }
         }
         __syncthreads();
@@ -449,12 +466,12 @@ __global__ void __launch_bounds__(512) k_medium(Cols src, Cols dst, const float*
     __syncthreads();
     const int shift = s_shift;
     const unsigned long long want = s_prefix >> shift;
-    const unsigned wantkey_hi = shift >= 32 ? 0u : (unsigned)(s_prefix >> 32);
+    const unsigned nodekey = (unsigned)(s_prefix >> 32);  // complete only when shift < 32
     // side of element i: -1 left, 0 node, 1 right.  The index is read only when the key alone cannot decide.
     auto classify = [&](unsigned i, unsigned key, unsigned& id, bool& have_id) -> int {
         have_id = false;
         id = 0;
-        if (shift < 32 && key == wantkey_hi) { id = (unsigned)src.idx[lo + i]; have_id = true; }
+        if (shift < 32 && key == nodekey) { id = (unsigned)src.idx[lo + i]; have_id = true; }
         const unsigned long long c = composite(key, id) >> shift;
         return c < want ? -1 : (c > want ? 1 : 0);
     };
@@ -466,7 +483,8 @@ __global__ void __launch_bounds__(512) k_medium(Cols src, Cols dst, const float*
         const unsigned key = skey[i];
         if (classify(i, key, id, have) == -1) { kmax = any_left ? max(kmax, key) : key; any_left = true; }
     }
-    if (any_left) atomicMax(&s_kmax, kmax);
+    for (int o = 16; o > 0; o >>= 1) kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
+    if (lane == 0 && kmax) atomicMax(&s_kmax, kmax);
     __syncthreads();
     kmax = s_kmax;
     for (unsigned i = tid; i < free_n; i += B) {
@@ -479,56 +497,63 @@ __global__ void __launch_bounds__(512) k_medium(Cols src, Cols dst, const float*
     }
     __syncthreads();
     const unsigned pmax = (unsigned)(s_best & 0xffffffffull);  // position (inside the range) of the left maximum
-    // ---- move the points ----
+    // ---- move the points: loads of four elements per thread are issued before any of them is ranked ----
     if (tid == 0) {  // the pinned element keeps its slot: last of the right range
         const unsigned p = lo + n - 1;
 #pragma unroll
         for (int c = 0; c < NCOL; ++c) dst.c[c][p] = src.c[c][p];
         dst.idx[p] = src.idx[p];
     }
-    const unsigned iters = (free_n + B - 1) / B;
-    for (unsigned it = 0; it < iters; ++it) {
-        const unsigned i = it * B + tid;
-        const bool valid = i < free_n;
-        float val[NCOL > 0 ? NCOL : 1];
-        int id = 0;
-        int side = 2;
-        if (valid) {
-            id = src.idx[lo + i];
+    constexpr int U = 4;
+    for (unsigned it = 0; it < iters; it += U) {
+        float val[U][NCOL > 0 ? NCOL : 1];
+        int id[U];
 #pragma unroll
-            for (int c = 0; c < NCOL; ++c) val[c] = src.c[c][lo + i];
-            const unsigned long long c = composite(skey[i], (unsigned)id) >> shift;
-            side = c < want ? -1 : (c > want ? 1 : 0);
-            if (i == pmax) side = -2;  // the left maximum: goes to the left range's last slot
-        }
-        const unsigned bl = __ballot_sync(0xffffffffu, side == -1);
-        const unsigned br = __ballot_sync(0xffffffffu, side == 1);
-        unsigned wl = 0, wr = 0;
-        if (lane == 0) {
-            if (bl) wl = atomicAdd(&s_cur[0], __popc(bl));
-            if (br) wr = atomicAdd(&s_cur[1], __popc(br));
-        }
-        wl = __shfl_sync(0xffffffffu, wl, 0);
-        wr = __shfl_sync(0xffffffffu, wr, 0);
-        const unsigned lt = (1u << lane) - 1u;
-        if (side == 2) continue;
-        if (side == 0) {  // the node: final slot lo + n/2 in every replica of the tree arrays
-            for (int r = 0; r < out.n; ++r) {
-                out.perm[r][out_lo + lo + m] = id;
-                if (out.tp[r]) {
+        for (int u = 0; u < U; ++u) {
+            const unsigned i = (it + u) * B + tid;
+            const bool valid = i < free_n;
+            id[u] = valid ? src.idx[lo + i] : 0;
 #pragma unroll
-                    for (int c = 0; c < NCOL; ++c) out.tp[r][(size_t)(out_lo + lo + m) * dim + c] = val[c];
-                }
+            for (int c = 0; c < NCOL; ++c) val[u][c] = valid ? src.c[c][lo + i] : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const unsigned i = (it + u) * B + tid;
+            int side = 2;
+            if (i < free_n) {
+                const unsigned long long c = composite(skey[i], (unsigned)id[u]) >> shift;
+                side = c < want ? -1 : (c > want ? 1 : 0);
+                if (i == pmax) side = -2;  // the left maximum: goes to the left range's last slot
             }
-            continue;
-        }
-        unsigned p;
-        if (side == -2) p = lo + m - 1;
-        else if (side == -1) p = lo + wl + __popc(bl & lt);
-        else p = lo + m + 1 + wr + __popc(br & lt);
+            const unsigned bl = __ballot_sync(0xffffffffu, side == -1);
+            const unsigned br = __ballot_sync(0xffffffffu, side == 1);
+            unsigned wl = 0, wr = 0;
+            if (lane == 0) {
+                if (bl) wl = atomicAdd(&s_cur[0], __popc(bl));
+                if (br) wr = atomicAdd(&s_cur[1], __popc(br));
+            }
+            wl = __shfl_sync(0xffffffffu, wl, 0);
+            wr = __shfl_sync(0xffffffffu, wr, 0);
+            const unsigned lt = (1u << lane) - 1u;
+            if (side == 2) continue;
+            if (side == 0) {  // the node: final slot lo + n/2 in every replica of the tree arrays
+                for (int r = 0; r < out.n; ++r) {
+                    out.perm[r][out_lo + lo + m] = id[u];
+                    if (out.tp[r]) {
 #pragma unroll
-        for (int c = 0; c < NCOL; ++c) dst.c[c][p] = val[c];
-        dst.idx[p] = id;
+                        for (int c = 0; c < NCOL; ++c) out.tp[r][(size_t)(out_lo + lo + m) * dim + c] = val[u][c];
+                    }
+                }
+                continue;
+            }
+            unsigned p;
+            if (side == -2) p = lo + m - 1;
+            else if (side == -1) p = lo + wl + __popc(bl & lt);
+            else p = lo + m + 1 + wr + __popc(br & lt);
+#pragma unroll
+            for (int c = 0; c < NCOL; ++c) dst.c[c][p] = val[u][c];
+            dst.idx[p] = id[u];
+        }
     }
 }
 
@@ -789,7 +814,7 @@ int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, u
     while (skip < finish_level && (n >> (finish_level - skip - 1)) <= kFinishT) ++skip;
     {
         cudaError_t e = cudaSuccess;
-#define KD_MED_ATTR(NC) if (e == cudaSuccess) e = cudaFuncSetAttribute(k_medium<NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)medium_smem_bytes())
+#define KD_MED_ATTR(NC) if (e == cudaSuccess) e = cudaFuncSetAttribute(k_medium<NC, 11>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)medium_smem_bytes())
         KD_MED_ATTR(0); KD_MED_ATTR(1); KD_MED_ATTR(2); KD_MED_ATTR(3); KD_MED_ATTR(4);
 #undef KD_MED_ATTR
         if (e != cudaSuccess) return fail(std::string("kd build: cudaFuncSetAttribute: ") + cudaGetErrorString(e));
@@ -814,8 +839,17 @@ int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, u
             const int64_t seg_n = n >> level;
             const int block = seg_n > 4096 ? 512 : (seg_n > 1024 ? 256 : 128);
             const unsigned cap = (unsigned)((seg_n + 31) & ~31ll);   // shared memory sized to the level's ranges
-            const size_t msmem = (size_t)cap * 4 + (size_t)kDigitBins * 4;
-#define KD_MED(NC) k_medium<NC><<<(unsigned)nseg, block, msmem, stream>>>(buf[cur], buf[cur ^ 1], keys, axis, out, out_lo, dim, N, level, cap, sc.err)
+            const bool narrow = seg_n <= 4096;   // 8-bit digits for the small ranges
+            const size_t msmem = (size_t)cap * 4 + (size_t)(narrow ? 256 : kDigitBins) * 4;
+#define KD_MED(NC)                                                                                                  \
+    do {                                                                                                            \
+        if (narrow)                                                                                                 \
+            k_medium<NC, 8><<<(unsigned)nseg, block, msmem, stream>>>(buf[cur], buf[cur ^ 1], keys, axis, out, out_lo, \
+                                                                      dim, N, level, cap, sc.err);                  \
+        else                                                                                                        \
+            k_medium<NC, 11><<<(unsigned)nseg, block, msmem, stream>>>(buf[cur], buf[cur ^ 1], keys, axis, out,      \
+                                                                       out_lo, dim, N, level, cap, sc.err);         \
+    } while (0)
             switch (ncol) {
                 case 0: KD_MED(0); break;
                 case 1: KD_MED(1); break;
