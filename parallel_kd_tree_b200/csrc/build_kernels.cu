@@ -572,39 +572,37 @@ constexpr int kFinishEpt = kFinishT / kFinishBlock;
 constexpr unsigned kInfKey = 0xffffffffu, kInfSlot = 0xffffu;
 static_assert(kFinishEpt == 8, "the finisher network is written for 8 elements per thread");
 
-// "other sorts before mine" under (key, point index).  Keys differ almost always; a real tie needs the
-// indices from shared memory and takes the (warp-uniform) slow path.  Padding (kInfKey) never ties.
-__device__ __noinline__ bool fin_tie_before(unsigned as, unsigned bs, const int32_t* sidx) { return sidx[as] < sidx[bs]; }
+// Compare-exchange on (key, point index, slot) triples.  (key, index) is a strict total order, so no tie
+// path exists: two 32-bit compares, one predicate op, three selects.  Padding is (kInfKey, 0xffffffff, kInfSlot);
+// two paddings compare equal and may be "swapped", which changes nothing.
+__device__ __forceinline__ bool fin_before(unsigned ak, unsigned ai, unsigned bk, unsigned bi) {
+    return (((unsigned long long)ak << 32) | ai) < (((unsigned long long)bk << 32) | bi);
+}
 
-// compare-exchange against a partner value: keep the smaller (keep_min) or the larger element
-__device__ __forceinline__ void fin_ce_partner(unsigned& key, unsigned& slot, unsigned ok, unsigned os, bool keep_min,
-                                               const int32_t* __restrict__ sidx) {
-    bool take = keep_min ? (ok < key) : (ok > key);
-    const bool tie = (ok == key) && (key != kInfKey);
-    if (__any_sync(0xffffffffu, tie)) {
-        if (tie) take = fin_tie_before(os, slot, sidx) == keep_min;
-    }
+// keep the smaller (keep_min) or the larger of (mine, partner's)
+__device__ __forceinline__ void fin_ce_partner(unsigned& key, unsigned& idx, unsigned& slot, unsigned ok, unsigned oi,
+                                               unsigned os, bool keep_min) {
+    const bool take = fin_before(ok, oi, key, idx) == keep_min;
     key = take ? ok : key;
+    idx = take ? oi : idx;
     slot = take ? os : slot;
 }
 
 template <int S>
-__device__ __forceinline__ void fin_reg_step(unsigned (&key)[8], unsigned (&slot)[8], unsigned vbase, unsigned k,
-                                             bool last, const int32_t* __restrict__ sidx) {
+__device__ __forceinline__ void fin_reg_step(unsigned (&key)[8], unsigned (&idx)[8], unsigned (&slot)[8], unsigned vbase,
+                                             unsigned k, bool last) {
     const bool asc_hi = last || ((vbase & k) == 0u);  // k >= 8: the direction bit lives in the thread index
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
         if (e & S) continue;
         const int f = e | S;
         const bool asc = k >= 8u ? asc_hi : (last || ((e & k) == 0u));
-        bool sw = asc ? (key[f] < key[e]) : (key[f] > key[e]);
-        const bool tie = (key[f] == key[e]) && (key[e] != kInfKey);
-        if (__any_sync(0xffffffffu, tie)) {
-            if (tie) sw = fin_tie_before(slot[f], slot[e], sidx) == asc;
-        }
-        const unsigned ke = key[e], kf = key[f], se = slot[e], sf = slot[f];
+        const unsigned ke = key[e], kf = key[f], ie = idx[e], jf = idx[f], se = slot[e], sf = slot[f];
+        const bool sw = fin_before(kf, jf, ke, ie) == asc;  // out of order for this direction
         key[e] = sw ? kf : ke;
         key[f] = sw ? ke : kf;
+        idx[e] = sw ? jf : ie;
+        idx[f] = sw ? ie : jf;
         slot[e] = sw ? sf : se;
         slot[f] = sw ? se : sf;
     }
@@ -658,35 +656,42 @@ __global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, 
         unsigned P = 2;
         int logP = 1;
         while (P < maxsort) { P <<= 1; ++logP; }
-        unsigned key[8], slot[8], pos[8];
+        unsigned key[8], idx[8], slot[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
             const unsigned v = vbase + e, sub = v >> logP, i = v & (P - 1u);
             const unsigned tb = sub < nsub ? stab[sub] : 0u;
             const unsigned sn = tb & 0xffffu, slo = tb >> 16;
             key[e] = kInfKey;
+            idx[e] = 0xffffffffu;
             slot[e] = kInfSlot;
-            pos[e] = 0xffffffffu;
             if (sn >= 3u && i + 1u < sn) {  // position i of the sub-range's first n-1 (the last slot is pinned)
-                pos[e] = slo + i;
-                slot[e] = sord[pos[e]];
-                const float f = ncol ? scol[axis * T + slot[e]] : pts[(size_t)sidx[slot[e]] * dim + axis];
+                slot[e] = sord[slo + i];
+                idx[e] = (unsigned)sidx[slot[e]];
+                const float f = ncol ? scol[axis * T + slot[e]] : pts[(size_t)idx[e] * dim + axis];
                 key[e] = ordered_key(f);
             }
         }
         for (unsigned k = 2; k <= P; k <<= 1) {
             const bool last = k == P;  // the final merge of every sub-range is ascending
             unsigned s = k >> 1;
-            for (; s >= 256u; s >>= 1) {  // partner in another warp: through shared memory
+            for (; s >= 256u; s >>= 1) {  // partner in another warp: through shared memory (keys+slots, then indices)
+                const unsigned d = s >> 3, pt = tid ^ d;
+                const bool keep_min = ((tid & d) == 0u) == (last || ((vbase & k) == 0u));
+                unsigned ok[8], os[8];
 #pragma unroll
                 for (int e = 0; e < 8; ++e) { xkey[e * kFinishBlock + tid] = key[e]; xslot[e * kFinishBlock + tid] = (unsigned short)slot[e]; }
                 __syncthreads();
-                const unsigned d = s >> 3, pt = tid ^ d;
-                const bool keep_min = ((tid & d) == 0u) == (last || ((vbase & k) == 0u));
+#pragma unroll
+                for (int e = 0; e < 8; ++e) { ok[e] = xkey[e * kFinishBlock + pt]; os[e] = xslot[e * kFinishBlock + pt]; }
+                __syncthreads();
+#pragma unroll
+                for (int e = 0; e < 8; ++e) xkey[e * kFinishBlock + tid] = idx[e];
+                __syncthreads();
 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
-                    const unsigned ok = xkey[e * kFinishBlock + pt], os = xslot[e * kFinishBlock + pt];
-                    fin_ce_partner(key[e], slot[e], ok, os, keep_min, sidx);
+                    const unsigned oi = xkey[e * kFinishBlock + pt];
+                    fin_ce_partner(key[e], idx[e], slot[e], ok[e], oi, os[e], keep_min);
                 }
                 __syncthreads();
             }
@@ -696,17 +701,24 @@ __global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, 
 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
                     const unsigned ok = __shfl_xor_sync(0xffffffffu, key[e], d);
+                    const unsigned oi = __shfl_xor_sync(0xffffffffu, idx[e], d);
                     const unsigned os = __shfl_xor_sync(0xffffffffu, slot[e], d);
-                    fin_ce_partner(key[e], slot[e], ok, os, keep_min, sidx);
+                    fin_ce_partner(key[e], idx[e], slot[e], ok, oi, os, keep_min);
                 }
             }
-            if (s == 4u) { fin_reg_step<4>(key, slot, vbase, k, last, sidx); s = 2u; }
-            if (s == 2u) { fin_reg_step<2>(key, slot, vbase, k, last, sidx); s = 1u; }
-            fin_reg_step<1>(key, slot, vbase, k, last, sidx);
+            if (s == 4u) { fin_reg_step<4>(key, idx, slot, vbase, k, last); s = 2u; }
+            if (s == 2u) { fin_reg_step<2>(key, idx, slot, vbase, k, last); s = 1u; }
+            fin_reg_step<1>(key, idx, slot, vbase, k, last);
         }
+        // sorted elements go back to the positions this thread's virtual slots stand for (padding has sunk
+        // to the end of every sub-range's block and is dropped)
 #pragma unroll
-        for (int e = 0; e < 8; ++e)
-            if (pos[e] != 0xffffffffu) sord[pos[e]] = (unsigned short)slot[e];
+        for (int e = 0; e < 8; ++e) {
+            const unsigned v = vbase + e, sub = v >> logP, i = v & (P - 1u);
+            const unsigned tb = sub < nsub ? stab[sub] : 0u;
+            const unsigned sn = tb & 0xffffu, slo = tb >> 16;
+            if (sn >= 3u && i + 1u < sn) sord[slo + i] = (unsigned short)slot[e];
+        }
         // next sub-level's table: range s -> 2s (left n/2) and 2s+1 (right n-n/2-1), the node slot drops out
         if ((n >> (j + 1)) >= 3u) {
             unsigned ent[2];
