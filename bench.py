@@ -124,6 +124,57 @@ def run_reference(args) -> dict:
     }
 
 
+def run_nccl_baseline(args) -> dict:
+    """The GPU baseline BASELINE.json asks for: the same tree with NCCL collectives + torch.sort
+    (parallel/nccl_baseline.py; none of this library's kernels)."""
+    import torch
+    import torch.distributed as dist
+
+    import parallel_kd_tree_b200 as kd
+    from parallel_kd_tree_b200.parallel import nccl_baseline as nb
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    n, dim = 1 << args.log2n, args.dim
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    first, local = kd.models.slice_bounds(n, world, rank)
+    pts = kd.ops.generate_uniform(args.seed, dim, local, first).to(dev)
+
+    def step():
+        return nb.nccl_build(pts, n) if world > 1 else nb.sort_build(pts)
+
+    steps, warm = max(1, min(args.steps, 3)), 1
+    for _ in range(warm):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        perm = step()
+    b.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([a.elapsed_time(b) / steps], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    out = {"impl": "nccl-baseline", "metric": "kd-tree build points/sec", "value": n / (ms * 1e-3), "unit": "points/s",
+           "n_gpus": world, "steps": steps, "warmup": warm, "ms_per_step": ms, "higher_is_better": True,
+           "scaling": "strong", "vs_baseline": n / (ms * 1e-3) / BASELINE_POINTS_PER_S, "dtype": "fp32",
+           "data": "synthetic",
+           "config": {"model": "same tree via NCCL all_reduce/all_to_all_single/all_gather_into_tensor + torch.sort",
+                      "n_points": n, "dim": dim, "seed": args.seed}, "gpu_launches": 0}
+    if world > 1:
+        dist.destroy_process_group()
+    return out
+
+
 def run_ours(args) -> dict:
     import torch
     import torch.distributed as dist
@@ -215,7 +266,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl-baseline"])
     ap.add_argument("--log2n", type=int, default=28)
     ap.add_argument("--dim", type=int, default=3)
     ap.add_argument("--dist", default="uniform", choices=["uniform", "clustered"])
@@ -227,7 +278,7 @@ def main():
         if int(os.environ.get("RANK", "0")) == 0:
             print(json.dumps(run_reference(args)), flush=True)
         return
-    out = run_ours(args)
+    out = run_nccl_baseline(args) if args.impl == "nccl-baseline" else run_ours(args)
     if int(os.environ.get("RANK", "0")) == 0:
         print(json.dumps(out), flush=True)
 

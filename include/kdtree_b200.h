@@ -94,7 +94,7 @@ int kd_bbox_gpu(const float* points, int64_t n, int dim, float* out_min, float* 
  * Every rank owns a "symmetric heap" of kd_dist_heap_bytes() bytes with the same layout; heap[r] is rank r's
  * heap as addressable from the calling rank (CUDA IPC mapping, or plain pointers for W virtual ranks on one GPU).
  * The tree arrays live inside the heap at the offsets reported by kd_dist_offsets().  world must be 1, 2, 4 or 8,
- * dim <= 4. */
+ * dim <= 8. */
 typedef struct {
     int world, rank, dim, with_tree_points;
     int64_t n_total;

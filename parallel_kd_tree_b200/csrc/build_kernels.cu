@@ -369,7 +369,7 @@ __global__ void __launch_bounds__(256) k_fixup(Cols dst, int ncol, const MaxRec*
 // points once out.
 // ------------------------------------------------------------------------------------------
 template <int NCOL, int DBITS>
-__global__ void __launch_bounds__(512, 3) k_medium(Cols src, Cols dst, const float* __restrict__ keys, int axis,
+__global__ void __launch_bounds__(512, (NCOL <= 4 ? 3 : 1)) k_medium(Cols src, Cols dst, const float* __restrict__ keys, int axis,
                                                 OutPtrs out, unsigned out_lo, int dim, unsigned N, int level,
                                                 unsigned cap, int* err) {
     // digit schedule over the 64-bit composite: 11/11/10 + 11/11/10 bits (as in k_hist) for the larger
@@ -828,6 +828,7 @@ int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, u
         cudaError_t e = cudaSuccess;
 #define KD_MED_ATTR(NC) if (e == cudaSuccess) e = cudaFuncSetAttribute(k_medium<NC, 11>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)medium_smem_bytes())
         KD_MED_ATTR(0); KD_MED_ATTR(1); KD_MED_ATTR(2); KD_MED_ATTR(3); KD_MED_ATTR(4);
+        KD_MED_ATTR(5); KD_MED_ATTR(6); KD_MED_ATTR(7); KD_MED_ATTR(8);
 #undef KD_MED_ATTR
         if (e != cudaSuccess) return fail(std::string("kd build: cudaFuncSetAttribute: ") + cudaGetErrorString(e));
     }
@@ -867,7 +868,11 @@ int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, u
                 case 1: KD_MED(1); break;
                 case 2: KD_MED(2); break;
                 case 3: KD_MED(3); break;
-                default: KD_MED(4); break;
+                case 4: KD_MED(4); break;
+                case 5: KD_MED(5); break;
+                case 6: KD_MED(6); break;
+                case 7: KD_MED(7); break;
+                default: KD_MED(8); break;
             }
 #undef KD_MED
             KD_LAUNCH_CHECK("k_medium");
@@ -907,7 +912,11 @@ int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, u
                 case 1: KD_PART(1); break;
                 case 2: KD_PART(2); break;
                 case 3: KD_PART(3); break;
-                default: KD_PART(4); break;
+                case 4: KD_PART(4); break;
+                case 5: KD_PART(5); break;
+                case 6: KD_PART(6); break;
+                case 7: KD_PART(7); break;
+                default: KD_PART(8); break;
             }
 #undef KD_PART
         }

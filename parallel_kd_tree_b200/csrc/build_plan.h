@@ -5,7 +5,7 @@
 
 namespace kd {
 
-constexpr int kMaxCarry = 4;      // dim <= kMaxCarry: coordinates travel with the points (SoA columns);
+constexpr int kMaxCarry = 8;      // dim <= kMaxCarry: coordinates travel with the points (SoA columns);
                                   // larger dim: only indices move and keys are gathered per level
 constexpr int kFinishT = 4096;    // ranges of at most this many points are finished in shared memory
 constexpr int kFinishEff = 512;     // select/partition levels go on until ranges have at most this many points

@@ -648,7 +648,11 @@ static int run_phase(const HostCtx& H, int level, int phase, int pass, unsigned 
                 case 1: k_partition_dist<1, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
                 case 2: k_partition_dist<2, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
                 case 3: k_partition_dist<3, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
-                default: k_partition_dist<4, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
+                case 4: k_partition_dist<4, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
+                case 5: k_partition_dist<5, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
+                case 6: k_partition_dist<6, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
+                case 7: k_partition_dist<7, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
+                default: k_partition_dist<8, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
             }
             KD_DLAUNCH("k_partition_dist");
             break;
@@ -729,7 +733,7 @@ static int fill_ctx(const kd_dist_ctx* c, kd::HostCtx& H) {
     if (!c) return kd::fail("kd_dist: null context");
     if (c->world < 1 || c->world > kd::kMaxWorld || (c->world & (c->world - 1))) return kd::fail("kd_dist: world must be 1, 2, 4 or 8");
     if (c->rank < 0 || c->rank >= c->world) return kd::fail("kd_dist: bad rank");
-    if (c->dim < 1 || c->dim > kd::kMaxCarry) return kd::fail("kd_dist: the distributed build supports dim <= 4");
+    if (c->dim < 1 || c->dim > kd::kMaxCarry) return kd::fail("kd_dist: the distributed build supports dim <= 8");
     if (c->n_total < 64ll * c->world || c->n_total >= (1ll << 31))
         return kd::fail("kd_dist: need 64 * world <= n_total < 2^31");
     H.P.world = c->world;

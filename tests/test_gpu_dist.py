@@ -35,3 +35,22 @@ def test_emulated_ranks_heavy_ties_and_rebuild(kd):
         torch.cuda.synchronize()
         for perm, _ in outs:
             assert torch.equal(perm.cpu(), ref)
+
+
+def test_emulated_ranks_eight_dimensions(kd):
+    # BASELINE.json config 5 shape (8-D): coordinates travel in eight columns
+    from parallel_kd_tree_b200.parallel.dist_build import EmulatedDistBuild
+    n, dim = 150000, 8
+    pts = kd.ops.generate_uniform(4, dim, n)
+    ref = kd.ops.build(pts)[0]
+    for world in (2, 8):
+        outs = EmulatedDistBuild(n, dim, world).build(pts)
+        torch.cuda.synchronize()
+        assert torch.equal(outs[0][0].cpu(), ref) and torch.equal(outs[-1][0].cpu(), ref)
+        assert torch.equal(outs[0][1].cpu(), pts[ref.long()])
+
+
+def test_library_sort_baseline_on_gpu_matches(kd):
+    from parallel_kd_tree_b200.parallel.nccl_baseline import sort_build
+    pts = kd.ops.generate_uniform(2, 3, 200000)
+    assert torch.equal(sort_build(pts.cuda()).cpu(), kd.ops.build(pts)[0])
