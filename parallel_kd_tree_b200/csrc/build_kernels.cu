@@ -735,16 +735,24 @@ __global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, 
         }
         __syncthreads();
     }
-    // every replica of the tree arrays receives this range: the sub-tree all-gather is fused into the store
+    // Every replica of the tree arrays receives this window: the sub-tree all-gather is fused into the store.
+    // Both arrays are written as flat runs (consecutive threads -> consecutive 4-byte words), so a warp emits
+    // whole 128-byte lines, which is what NVLink wants for the remote replicas.  Slots of nodes placed by
+    // earlier levels are skipped (they already hold their final value everywhere).
+    const unsigned total = ncol ? n * (unsigned)dim : 0u;
     for (int r = 0; r < out.n; ++r) {
-        int32_t* __restrict__ perm = out.perm[r];
-        float* __restrict__ tree_pts = out.tp[r];
+        int32_t* __restrict__ perm = out.perm[r] + out_lo + lo;
+        float* __restrict__ tree_pts = out.tp[r] ? out.tp[r] + (size_t)(out_lo + lo) * dim : nullptr;
         for (unsigned p = tid; p < n; p += kFinishBlock) {
-            unsigned slot = sord[p];
-            if (slot == kInfSlot) continue;  // a node placed by an earlier level
-            perm[out_lo + lo + p] = sidx[slot];
-            if (tree_pts && ncol)
-                for (int c = 0; c < ncol; ++c) tree_pts[(size_t)(out_lo + lo + p) * dim + c] = scol[c * T + slot];
+            const unsigned slot = sord[p];
+            if (slot != kInfSlot) perm[p] = sidx[slot];
+        }
+        if (tree_pts) {
+            for (unsigned f = tid; f < total; f += kFinishBlock) {
+                const unsigned p = f / (unsigned)dim, c = f - p * (unsigned)dim;
+                const unsigned slot = sord[p];
+                if (slot != kInfSlot) tree_pts[f] = scol[c * T + slot];
+            }
         }
     }
 }

@@ -1,0 +1,99 @@
+"""Per-level timing of the distributed build's fused paths (BASELINE.json config 5: "per-level exchange GB/s
+sweep against 900 GB/s per direction").  torchrun --nproc-per-node W tools/exchange_sweep.py [log2n] [dim]
+
+For every distributed level: device time of the select (histogram passes + one-shot P2P reduction + scans) and
+of the partition-to-peer kernel, the bytes that kernel pushes over NVLink from this GPU, and the resulting
+GB/s per direction per GPU.  Then the local phase (whose stores are replicated into every GPU = the all-gather).
+Times are max over ranks (CUDA events)."""
+import ctypes as C
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+
+import parallel_kd_tree_b200 as kd
+from parallel_kd_tree_b200.parallel import dist_build as db
+
+rank, world, local_rank = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local_rank)
+dev = torch.device("cuda", local_rank)
+os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+dist.init_process_group("nccl", device_id=dev)
+log2n = int(sys.argv[1]) if len(sys.argv) > 1 else 24
+dim = int(sys.argv[2]) if len(sys.argv) > 2 else 8
+n = 1 << log2n
+first, local = kd.models.slice_bounds(n, world, rank)
+pts = kd.ops.generate_uniform(1, dim, local, first).to(dev)
+b = db.IpcDistBuild(n, dim, with_tree_points=True)
+L = kd.lib()
+st = torch.cuda.current_stream().cuda_stream
+levels = world.bit_length() - 1
+
+
+def ev():
+    return torch.cuda.Event(enable_timing=True)
+
+
+def run(record):
+    b.serial += 1
+    b.load(pts)
+    for level in range(levels):
+        e0, e1, e2, e3 = ev(), ev(), ev(), ev()
+        e0.record()
+        kd._lib.check(L.kd_dist_phase(C.byref(b.ctx), level, db.PH_STATE, 0, b.serial, st), "state")
+        for d in range(6):
+            kd._lib.check(L.kd_dist_phase(C.byref(b.ctx), level, db.PH_HIST, d, b.serial, st), "hist")
+            kd._lib.check(L.kd_dist_phase(C.byref(b.ctx), level, db.PH_SCAN, d, b.serial, st), "scan")
+        for ph in (db.PH_CNT_POST, db.PH_CNT_WAIT):
+            kd._lib.check(L.kd_dist_phase(C.byref(b.ctx), level, ph, 7, b.serial, st), "cnt")
+        e1.record()
+        kd._lib.check(L.kd_dist_phase(C.byref(b.ctx), level, db.PH_PART, 7, b.serial, st), "part")
+        e2.record()
+        for ph in range(db.PH_PART_POST, db.PH_FIX_WAIT + 1):
+            kd._lib.check(L.kd_dist_phase(C.byref(b.ctx), level, ph, 7, b.serial, st), "sync")
+        e3.record()
+        record.append((level, e0, e1, e2, e3))
+    e4, e5 = ev(), ev()
+    e4.record()
+    kd._lib.check(L.kd_dist_local_build(C.byref(b.ctx), st), "local")
+    kd._lib.check(L.kd_dist_done(C.byref(b.ctx), 1, b.serial, st), "done")
+    kd._lib.check(L.kd_dist_done(C.byref(b.ctx), 0, b.serial, st), "done")
+    e5.record()
+    record.append(("local", e4, e5))
+
+
+run([])
+torch.cuda.synchronize(); dist.barrier()
+rec = []
+run(rec)
+torch.cuda.synchronize()
+b.status()
+rows = []
+for r in rec:
+    if r[0] == "local":
+        t = torch.tensor([r[1].elapsed_time(r[2])], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        nloc = n // world
+        out_bytes = nloc * 4 * (1 + dim) * (world - 1)       # perm + tree_points slices stored into every other GPU
+        rows.append({"phase": "local build + fused all-gather", "ms": round(float(t), 3),
+                     "nvlink_bytes_out_per_gpu": out_bytes,
+                     "note": "lower bound of the replication alone at 770 GB/s: %.3f ms" % (out_bytes / 770e9 * 1e3)})
+        continue
+    level, e0, e1, e2, e3 = r
+    G = world >> level
+    t = torch.tensor([e0.elapsed_time(e1), e1.elapsed_time(e2), e2.elapsed_time(e3)], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    nloc = n // world
+    out_bytes = int(nloc * (1 - 1 / G) * 4 * (dim + 1))      # expected share of my points whose owner is another GPU
+    gbs = out_bytes / (float(t[1]) * 1e-3) / 1e9
+    rows.append({"level": level, "group": G, "select_ms": round(float(t[0]), 3), "partition_ms": round(float(t[1]), 3),
+                 "sync_fixup_ms": round(float(t[2]), 3), "nvlink_bytes_out_per_gpu": out_bytes,
+                 "exchange_GBps_per_direction": round(gbs, 1), "frac_of_770_measured": round(gbs / 770, 3),
+                 "frac_of_900_nominal": round(gbs / 900, 3)})
+if rank == 0:
+    print(json.dumps({"n": n, "dim": dim, "world": world, "rows": rows}, indent=1))
+b.close()
+dist.destroy_process_group()
