@@ -366,6 +366,9 @@ __global__ void k_counts_wait(DistParams P, LevelGeo g, unsigned long long epoch
 // K6: partition with P2P stores into the owners' next-level buffers
 template <int NCOL, int BLOCK, int IPT>
 __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo g, int cur, int axis, bool with_tp) {
+    extern __shared__ __align__(16) unsigned char pd_smem[];
+    float* stage = reinterpret_cast<float*>(pd_smem);                                  // [NCOL][BLOCK * IPT]
+    int* stage_idx = reinterpret_cast<int*>(stage + (size_t)NCOL * BLOCK * IPT);       // [BLOCK * IPT]
     __shared__ unsigned s_cnt[2], s_base[2];
     __shared__ unsigned long long s_wcomp[BLOCK / 32];
     __shared__ unsigned s_wpos[BLOCK / 32];
@@ -450,6 +453,8 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
         }
         __syncthreads();
         const unsigned baseL = Loff + s_base[0], baseR = Roff + s_base[1];
+        const unsigned nl = s_cnt[0], nrt = s_cnt[1];
+        // stage the tile in shared memory in output order (left run, then right run) ...
 #pragma unroll
         for (int k = 0; k < IPT; ++k) {
             if (side[k] == 2) continue;
@@ -461,17 +466,27 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
                 continue;
             }
             const bool left = side[k] == -1;
-            const unsigned o = (left ? baseL : baseR) + rk[k];
+            const unsigned si = left ? rk[k] : nl + rk[k];
+#pragma unroll
+            for (int c = 0; c < NCOL; ++c) stage[c * (BLOCK * IPT) + si] = val[k][c];
+            stage_idx[si] = id[k];
+            if (left) {
+                unsigned long long c = composite(key[k], (unsigned)id[k]);
+                if (!bestvalid || c > best) { best = c; bestpos = baseL + rk[k]; bestvalid = 1; }
+            }
+        }
+        __syncthreads();
+        // ... and push it out as two contiguous runs: consecutive threads -> consecutive remote slots, so a warp
+        // store is one whole 128-byte line on the owner GPU (owner changes at most a few times per run)
+        for (unsigned t = tid; t < nl + nrt; t += BLOCK) {
+            const bool left = t < nl;
+            const unsigned o = left ? baseL + t : baseR + (t - nl);
             unsigned mem, pos;
             owner_of(o, left ? m : nr, Gh, mem, pos);
             const Cols& d = dst[left ? mem : Gh + mem];
 #pragma unroll
-            for (int c = 0; c < NCOL; ++c) d.c[c][pos] = val[k][c];
-            d.idx[pos] = id[k];
-            if (left) {
-                unsigned long long c = composite(key[k], (unsigned)id[k]);
-                if (!bestvalid || c > best) { best = c; bestpos = o; bestvalid = 1; }
-            }
+            for (int c = 0; c < NCOL; ++c) d.c[c][pos] = stage[c * (BLOCK * IPT) + t];
+            d.idx[pos] = stage_idx[t];
         }
     }
     if (has_node) {
@@ -644,15 +659,21 @@ static int run_phase(const HostCtx& H, int level, int phase, int pass, unsigned 
             break;
         case PH_PART: {
             const int grid = dist_grid(local_cap, 2048);
+#define KD_PD(NC)                                                                                              \
+    do {                                                                                                       \
+        const size_t sm = (size_t)((NC) + 1) * 2048 * 4;                                                       \
+        cudaFuncSetAttribute(k_partition_dist<NC, 512, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm); \
+        k_partition_dist<NC, 512, 4><<<grid, 512, sm, st>>>(P, g, cur, axis, H.with_tp);                       \
+    } while (0)
             switch (P.ncol) {
-                case 1: k_partition_dist<1, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
-                case 2: k_partition_dist<2, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
-                case 3: k_partition_dist<3, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
-                case 4: k_partition_dist<4, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
-                case 5: k_partition_dist<5, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
-                case 6: k_partition_dist<6, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
-                case 7: k_partition_dist<7, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
-                default: k_partition_dist<8, 512, 4><<<grid, 512, 0, st>>>(P, g, cur, axis, H.with_tp); break;
+                case 1: KD_PD(1); break;
+                case 2: KD_PD(2); break;
+                case 3: KD_PD(3); break;
+                case 4: KD_PD(4); break;
+                case 5: KD_PD(5); break;
+                case 6: KD_PD(6); break;
+                case 7: KD_PD(7); break;
+                default: KD_PD(8); break;
             }
             KD_DLAUNCH("k_partition_dist");
             break;
