@@ -567,6 +567,42 @@ __global__ void __launch_bounds__(512, (NCOL <= 4 ? 3 : 1)) k_medium(Cols src, C
 // shared memory.  Points never move, a (key, slot) pair does; all slots are final at the end and
 // are written out once, coalesced.
 // ------------------------------------------------------------------------------------------
+// TMA (bulk async copy engine) helpers: 1-D global -> shared copies completing on an mbarrier.
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, unsigned bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(unsigned long long* bar, unsigned parity) {
+    unsigned ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// bounded wait: a copy that never completes must not hang the device (the caller falls back to plain loads)
+__device__ __forceinline__ bool mbar_wait(unsigned long long* bar, unsigned parity) {
+    for (unsigned i = 0; i < (1u << 20); ++i)
+        if (mbar_try_wait(bar, parity)) return true;
+    return false;
+}
+
 constexpr int kFinishBlock = 512;
 constexpr int kFinishEpt = kFinishT / kFinishBlock;
 constexpr unsigned kInfKey = 0xffffffffu, kInfSlot = 0xffffu;
@@ -616,17 +652,33 @@ __global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, 
     unsigned lo, n;
     seg_range(N, level, blockIdx.x, lo, n);
     if (n == 0) return;
-    float* scol = reinterpret_cast<float*>(smem);                         // [ncol][T]  coordinates by slot
-    int32_t* sidx = reinterpret_cast<int32_t*>(scol + (size_t)ncol * T);  // [T]        point index by slot
-    unsigned* xkey = reinterpret_cast<unsigned*>(sidx + T);               // [T]        exchange buffer (keys)
+    constexpr int TS = kFinishT + 8;  // column stride: the staged window starts at a 16-byte aligned element
+    float* scol = reinterpret_cast<float*>(smem);                         // [ncol][TS] coordinates by slot
+    int32_t* sidx = reinterpret_cast<int32_t*>(scol + (size_t)ncol * TS); // [TS]       point index by slot
+    unsigned* xkey = reinterpret_cast<unsigned*>(sidx + TS);              // [T]        exchange buffer (keys)
     unsigned* stab = xkey + T;                                            // [T/2]      sub-range table (lo << 16 | n)
     unsigned short* sord = reinterpret_cast<unsigned short*>(stab + T / 2);  // [T]     slot by position
     unsigned short* xslot = sord + T;                                     // [T]        exchange buffer (slots)
+    __shared__ __align__(8) unsigned long long fin_bar;
     const unsigned tid = threadIdx.x;
-    for (unsigned p = tid; p < n; p += kFinishBlock) {
-        sidx[p] = src.idx[lo + p];
-        for (int c = 0; c < ncol; ++c) scol[c * T + p] = src.c[c][lo + p];
-        sord[p] = (unsigned short)p;
+    // Stage the window with the TMA engine: one bulk copy per column (cp.async.bulk, completion counted in
+    // bytes on an mbarrier) instead of 512 threads issuing scalar loads.  Bulk copies need 16-byte aligned
+    // addresses and sizes, so the copy starts `delta` elements early and slots are offsets into that window.
+    const unsigned delta = lo & 3u, alo = lo - delta;
+    const unsigned bytes = ((delta + n + 3u) & ~3u) * 4u;
+    if (tid == 0) mbar_init(&fin_bar, 1);
+    __syncthreads();
+    if (tid == 0) {
+        mbar_expect_tx(&fin_bar, bytes * (unsigned)(ncol + 1));
+        for (int c = 0; c < ncol; ++c) tma_load_1d(scol + c * TS, src.c[c] + alo, bytes, &fin_bar);
+        tma_load_1d(sidx, src.idx + alo, bytes, &fin_bar);
+    }
+    for (unsigned p = tid; p < n; p += kFinishBlock) sord[p] = (unsigned short)(p + delta);
+    if (!__syncthreads_and(mbar_wait(&fin_bar, 0) ? 1 : 0)) {  // never expected; same data through the LSU instead
+        for (unsigned p = tid; p < n; p += kFinishBlock) {
+            sidx[delta + p] = src.idx[lo + p];
+            for (int c = 0; c < ncol; ++c) scol[c * TS + delta + p] = src.c[c][lo + p];
+        }
     }
     if (tid == 0) stab[0] = n;  // sub-range 0 of sub-level 0: lo = 0, size n
     __syncthreads();
@@ -668,7 +720,7 @@ __global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, 
             if (sn >= 3u && i + 1u < sn) {  // position i of the sub-range's first n-1 (the last slot is pinned)
                 slot[e] = sord[slo + i];
                 idx[e] = (unsigned)sidx[slot[e]];
-                const float f = ncol ? scol[axis * T + slot[e]] : pts[(size_t)idx[e] * dim + axis];
+                const float f = ncol ? scol[axis * TS + slot[e]] : pts[(size_t)idx[e] * dim + axis];
                 key[e] = ordered_key(f);
             }
         }
@@ -751,7 +803,7 @@ __global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, 
             for (unsigned f = tid; f < total; f += kFinishBlock) {
                 const unsigned p = f / (unsigned)dim, c = f - p * (unsigned)dim;
                 const unsigned slot = sord[p];
-                if (slot != kInfSlot) tree_pts[f] = scol[c * T + slot];
+                if (slot != kInfSlot) tree_pts[f] = scol[c * TS + slot];
             }
         }
     }
@@ -943,6 +995,7 @@ int build_gpu(const float* points, int64_t n, int dim, int32_t* perm, float* tre
     if (n >= (1ll << 31)) return fail("kd_build_gpu: n must be below 2^31");
     BuildPlan p = make_plan(n, dim);
     if (workspace_bytes < p.bytes) return fail("kd_build_gpu: workspace too small");
+    if (((uintptr_t)workspace & 255u) != 0) return fail("kd_build_gpu: the workspace must be 256-byte aligned");
     g_launches = 0;
     unsigned char* ws = (unsigned char*)workspace;
     Cols buf[2];

@@ -78,8 +78,8 @@ void reset_launches();
 inline size_t medium_smem_bytes() { return (size_t)kMediumMax * 4 + (size_t)2048 * 4; }
 
 inline size_t finish_smem_bytes(int ncol) {
-    // scol[ncol][T] f32, sidx[T] i32, xkey[T] u32, stab[T/2] u32, sord[T] u16, xslot[T] u16
-    return (size_t)ncol * kFinishT * 4 + (size_t)kFinishT * 4 * 2 + (size_t)kFinishT * 2 + (size_t)kFinishT * 2 * 2;
+    // scol[ncol][T+8] f32, sidx[T+8] i32, xkey[T] u32, stab[T/2] u32, sord[T] u16, xslot[T] u16
+    return (size_t)(ncol + 1) * (kFinishT + 8) * 4 + (size_t)kFinishT * 4 + (size_t)kFinishT * 2 + (size_t)kFinishT * 2 * 2;
 }
 
 }  // namespace kd
