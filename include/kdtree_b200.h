@@ -67,7 +67,7 @@ int kd_build_gpu(const float* points, int64_t n, int dim, int32_t* perm, float* 
 /* The same build for callers that cannot allocate device memory (code running inside someone else's fixed
  * memory plan, or where cudaMalloc and its implicit synchronisation are off limits): the scratch is a 16 MiB
  * array built into the library, so nothing is allocated and no workspace is passed.  Accepts only problems with
- * kd_build_workspace_bytes(n, dim) <= 16 MiB (about 500 000 3-D points) and fails with a message otherwise.
+ * kd_build_workspace_bytes(n, dim) <= 16 MiB (about 400 000 3-D points) and fails with a message otherwise.
  * The array is shared by all calls on a device and keeps the previous call's contents (the build re-zeroes what
  * it needs): calls that may overlap on the GPU race, serialise them.  The first call on each device resolves
  * the array's address; make it before any stream capture.  Every GPU that loads the library holds the 16 MiB

@@ -52,6 +52,12 @@ __global__ void k_state_init(SegState* st, unsigned N, int level, unsigned nseg)
     S.curR = 0;
     S.shift = 64;
     S.done = 0;
+    S.lowP = 0ull;
+    S.highP = ~0ull;
+    S.cL = 0;
+    S.cand_cnt = 0;
+    S.use_cand = 0;
+    S.pad_ = 0;
     st[s] = S;
 }
 
@@ -76,20 +82,159 @@ __device__ __forceinline__ void warp_hist_add(unsigned* sh, unsigned digit, bool
     if (valid && (__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&sh[digit], __popc(peers));
 }
 
+// ---- bracket select for large ranges -------------------------------------------------------------
+// A sorted sample of the range brackets the wanted rank between two pivots (k_sample); ONE pass over the
+// keys counts what lies below the bracket and copies what lies inside it (about a tenth of the range) to the
+// candidate arrays (k_bracket); the digit passes then run on the candidates only.  The result is exact: the
+// counts prove whether the wanted rank is inside the bracket, and if it is not (or for adversarial orderings
+// of the input) the range simply falls back to digit passes over all of its keys.
+constexpr int kSampleN = 1024;   // sample size per range
+constexpr int kSampleDelta = 72; // half-width of the bracket in sample ranks (4.5 sigma of a random sample's rank)
+
+__global__ void __launch_bounds__(512) k_sample(const float* __restrict__ keys, const int32_t* __restrict__ idx,
+                                                SegState* st, unsigned N, int level) {
+    __shared__ unsigned long long sm[kSampleN];
+    unsigned lo, n;
+    seg_range(N, level, blockIdx.x, lo, n);
+    const unsigned free_n = n - 1, m = n >> 1, tid = threadIdx.x;
+    for (unsigned k = tid; k < (unsigned)kSampleN; k += 512) {
+        const unsigned pos = lo + (unsigned)(((unsigned long long)k * free_n) / kSampleN);  // systematic sample
+        sm[k] = composite(ordered_key(keys[pos]), (unsigned)idx[pos]);
+    }
+    __syncthreads();
+    for (unsigned k = 2; k <= (unsigned)kSampleN; k <<= 1) {
+        for (unsigned j = k >> 1; j > 0; j >>= 1) {
+            const unsigned i = ((tid & ~(j - 1u)) << 1) | (tid & (j - 1u)), l = i | j;  // tid-th pair at distance j
+            const bool asc = (i & k) == 0u;
+            const unsigned long long a = sm[i], b = sm[l];
+            if ((a > b) == asc) { sm[i] = b; sm[l] = a; }
+            __syncthreads();
+        }
+    }
+    if (tid == 0) {
+        const int r = (int)(((unsigned long long)m * kSampleN) / free_n);
+        const int li = r - kSampleDelta, hi = r + kSampleDelta;
+        st[blockIdx.x].lowP = li < 0 ? 0ull : sm[li];
+        st[blockIdx.x].highP = hi >= kSampleN ? ~0ull : sm[hi];
+    }
+}
+
+// One streaming pass, no block-wide synchronisation: every CTA compacts the candidates of its chunk to the
+// chunk's own first slots of the candidate arrays (they can never overflow it) with warp-aggregated
+// shared-memory cursors, and publishes its count; the digit passes then visit (chunk start, count) per CTA.
+template <int BLOCK, int IPT>
+__global__ void __launch_bounds__(BLOCK) k_bracket(const float* __restrict__ keys, const int32_t* __restrict__ idx,
+                                                   SegState* st, float* __restrict__ cand_key,
+                                                   int32_t* __restrict__ cand_idx, unsigned* __restrict__ cand_cta,
+                                                   unsigned N, int level, int cps) {
+    __shared__ unsigned s_cur, s_less;
+    const unsigned s = blockIdx.x / cps, j = blockIdx.x % cps;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const unsigned long long lowP = st[s].lowP, highP = st[s].highP;
+    const unsigned lowK = (unsigned)(lowP >> 32), highK = (unsigned)(highP >> 32);
+    unsigned lo, n;
+    seg_range(N, level, s, lo, n);
+    const unsigned free_n = n - 1;
+    const unsigned chunk = (free_n + cps - 1) / cps;
+    const unsigned b = min(lo + j * chunk, lo + free_n), e = min(b + chunk, lo + free_n);
+    unsigned less = 0;
+    if (tid == 0) { s_cur = 0; s_less = 0; }
+    __syncthreads();
+    for (unsigned tb = b; tb < e; tb += BLOCK * IPT) {
+        float f[IPT];
+#pragma unroll
+        for (int k = 0; k < IPT; ++k) {
+            const unsigned i = tb + k * BLOCK + tid;
+            f[k] = i < e ? keys[i] : 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < IPT; ++k) {
+            const unsigned i = tb + k * BLOCK + tid;
+            const unsigned key = ordered_key(f[k]);
+            bool cand = false;
+            int id = 0;
+            if (i < e) {
+                if (key < lowK) ++less;
+                else if (key <= highK) {  // the index is needed only inside (or on the edge of) the bracket
+                    id = idx[i];
+                    const unsigned long long c = composite(key, (unsigned)id);
+                    if (c < lowP) ++less;
+                    else cand = c <= highP;
+                }
+            }
+            const unsigned bc = __ballot_sync(0xffffffffu, cand);
+            if (bc) {
+                unsigned w = 0;
+                if (lane == 0) w = atomicAdd(&s_cur, __popc(bc));
+                w = __shfl_sync(0xffffffffu, w, 0);
+                if (cand) {
+                    const unsigned p = b + w + __popc(bc & ((1u << lane) - 1u));
+                    cand_key[p] = f[k];
+                    cand_idx[p] = id;
+                }
+            }
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) less += __shfl_xor_sync(0xffffffffu, less, o);
+    if (lane == 0 && less) atomicAdd(&s_less, less);
+    __syncthreads();
+    if (tid == 0) {
+        cand_cta[blockIdx.x] = s_cur;
+        if (s_cur) atomicAdd(&st[s].cand_cnt, s_cur);
+        if (s_less) atomicAdd(&st[s].cL, s_less);
+    }
+}
+
+__global__ void k_bracket_finish(SegState* st, unsigned N, int level, unsigned nseg) {
+    const unsigned s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= nseg) return;
+    unsigned lo, n;
+    seg_range(N, level, s, lo, n);
+    const unsigned m = n >> 1, cL = st[s].cL, cc = st[s].cand_cnt;
+    if (m >= cL && m - cL < cc) {  // the wanted rank is inside the bracket: select rank m - cL among the candidates
+        st[s].use_cand = 1;
+        st[s].rank = m - cL;
+        st[s].cnt = cc;
+    }
+}
+
 template <int BLOCK, int UNROLL>
-__global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys, const int32_t* __restrict__ idx,
-                                                const SegState* __restrict__ st, unsigned* __restrict__ ghist,
-                                                unsigned N, int level, int cps, int d) {
+__global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys_all, const int32_t* __restrict__ idx_all,
+                                                const float* __restrict__ cand_key,
+                                                const int32_t* __restrict__ cand_idx,
+                                                const unsigned* __restrict__ cand_cta, SegState* st,
+                                                unsigned* __restrict__ ghist, unsigned N, int level, int cps, int d) {
     __shared__ unsigned sh[kDigitBins];
     unsigned s = blockIdx.x / cps, j = blockIdx.x % cps;
     SegState S = st[s];
-    if (S.done) return;
+    if (S.done == 1) return;
     unsigned lo, n;
     seg_range(N, level, s, lo, n);
-    unsigned free_n = n - 1;  // the pinned last slot never takes part (kdtree_sequential.cpp:46-48)
-    unsigned chunk = (free_n + cps - 1) / cps;
-    unsigned b = lo + j * chunk, e = min(b + chunk, lo + free_n);
+    // the pinned last slot never takes part (kdtree_sequential.cpp:46-48); after a successful bracket the
+    // passes run on the range's candidates instead of on all of its keys
+    const float* __restrict__ keys = S.use_cand ? cand_key : keys_all;
+    const int32_t* __restrict__ idx = S.use_cand ? cand_idx : idx_all;
+    const unsigned free_n = n - 1;
+    const unsigned chunk = (free_n + cps - 1) / cps;
+    const unsigned b = min(lo + j * chunk, lo + free_n);
+    // (k_bracket left this CTA's candidates at the first slots of the same chunk)
+    const unsigned e = S.use_cand ? b + cand_cta[blockIdx.x] : min(b + chunk, lo + free_n);
     if (b >= e) return;
+    if (S.done == 2) {
+        // exactly one candidate matches the prefix, but elements outside the bracket may share those bits:
+        // read the candidate back so that the partition compares complete composites
+        const int psh = S.shift;
+        for (unsigned i = b + threadIdx.x; i < e; i += BLOCK) {
+            const unsigned long long c = composite(ordered_key(keys[i]), (unsigned)idx[i]);
+            if ((c >> psh) == (S.prefix >> psh)) {
+                st[s].prefix = c;
+                st[s].shift = 0;
+                __threadfence();
+                st[s].done = 1;
+            }
+        }
+        return;
+    }
     for (int t = threadIdx.x; t < kDigitBins; t += BLOCK) sh[t] = 0;
     __syncthreads();
     const int dsh = digit_shift(d);
@@ -146,7 +291,7 @@ __global__ void __launch_bounds__(256) k_scan(SegState* st, unsigned* ghist, int
     __shared__ unsigned fcum, fcnt;
     unsigned s = blockIdx.x;
     SegState S = st[s];
-    if (S.done) return;
+    if (S.done) return;  // finished, or waiting for the candidate read-back of the next k_hist launch
     unsigned* h = ghist + (size_t)s * kDigitBins;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     if (tid == 0) fbin = -1;
@@ -184,7 +329,7 @@ __global__ void __launch_bounds__(256) k_scan(SegState* st, unsigned* ghist, int
             S.rank = r - fcum;
             S.cnt = fcnt;
             S.shift = digit_shift(d);
-            S.done = (fcnt == 1u || d == kNumDigits - 1) ? 1 : 0;
+            S.done = d == kNumDigits - 1 ? 1 : (fcnt == 1u ? (S.use_cand ? 2 : 1) : 0);
         }
         st[s] = S;
     }
@@ -847,6 +992,10 @@ BuildPlan make_plan(int64_t n, int dim) {
     p.off_hist = take((size_t)p.max_seg * kDigitBins * 4);
     p.off_rec = take((size_t)p.max_rec * 16);
     p.off_err = take(256);
+    // candidate arrays of the bracket select, only when there are large-range levels
+    p.off_ckey = lv > 0 ? take((size_t)n * 4) : 0;
+    p.off_cidx = lv > 0 ? take((size_t)n * 4) : 0;
+    p.off_ccta = take((size_t)p.max_rec * 4);
     p.bytes = off;
     return p;
 }
@@ -954,9 +1103,22 @@ int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, u
             KD_LAUNCH_CHECK("k_gather_keys");
             keys = sc.keybuf;
         }
+        const bool bracket = sc.cand_key != nullptr;
+        if (bracket) {
+            k_sample<<<(unsigned)nseg, 512, 0, stream>>>(keys, buf[cur].idx, sc.st, N, level);
+            KD_LAUNCH_CHECK("k_sample");
+            k_bracket<512, 4><<<(unsigned)(nseg * cps_p), 512, 0, stream>>>(keys, buf[cur].idx, sc.st, sc.cand_key,
+                                                                           sc.cand_idx, sc.cand_cta, N, level, cps_p);
+            KD_LAUNCH_CHECK("k_bracket");
+            k_bracket_finish<<<(unsigned)((nseg + 255) / 256), 256, 0, stream>>>(sc.st, N, level, (unsigned)nseg);
+            KD_LAUNCH_CHECK("k_bracket_finish");
+        }
+        // (a candidate read-back requested by pass d's scan is served by pass d+1's k_hist; pass 5 never asks)
         for (int d = 0; d < kNumDigits; ++d) {
-            k_hist<512, 4><<<(unsigned)(nseg * cps_h), 512, 0, stream>>>(keys, buf[cur].idx, sc.st, sc.ghist, N, level,
-                                                                        cps_h, d);
+            // with a bracket the passes use the bracket's CTA geometry (per-CTA candidate runs)
+            const int cps_d = bracket ? cps_p : cps_h;
+            k_hist<512, 4><<<(unsigned)(nseg * cps_d), 512, 0, stream>>>(keys, buf[cur].idx, sc.cand_key, sc.cand_idx,
+                                                                        sc.cand_cta, sc.st, sc.ghist, N, level, cps_d, d);
             KD_LAUNCH_CHECK("k_hist");
             k_scan<<<(unsigned)nseg, 256, 0, stream>>>(sc.st, sc.ghist, d, sc.err);
             KD_LAUNCH_CHECK("k_scan");
@@ -1009,6 +1171,9 @@ int build_gpu(const float* points, int64_t n, int dim, int32_t* perm, float* tre
     sc.ghist = (unsigned*)(ws + p.off_hist);
     sc.rec = (MaxRec*)(ws + p.off_rec);
     sc.err = (int*)(ws + p.off_err);
+    sc.cand_key = p.finish_level > 0 ? (float*)(ws + p.off_ckey) : nullptr;
+    sc.cand_idx = p.finish_level > 0 ? (int32_t*)(ws + p.off_cidx) : nullptr;
+    sc.cand_cta = (unsigned*)(ws + p.off_ccta);
     const unsigned N = (unsigned)n;
 
     if (cudaMemsetAsync(sc.ghist, 0, (size_t)p.max_seg * kDigitBins * 4, stream) != cudaSuccess ||

@@ -11,7 +11,7 @@
 // Consequences of the scratch being one static array:
 //   * every GPU on which the library's device code is loaded keeps those 16 MiB reserved until the
 //     process exits, whether or not this entry point is ever called;
-//   * the problem must fit: kd_build_workspace_bytes(n, dim) <= 16 MiB (about 500 000 points in
+//   * the problem must fit: kd_build_workspace_bytes(n, dim) <= 16 MiB (about 400 000 points in
 //     3-D).  Larger problems are refused with an error, nothing is launched;
 //   * all calls on one device use the same array and it keeps whatever the previous call left in
 //     it.  The build clears the parts it needs zeroed at the start of every call, so back-to-back

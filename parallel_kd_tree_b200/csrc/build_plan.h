@@ -18,7 +18,13 @@ struct SegState {
     unsigned int cnt;           // candidates matching the prefix
     unsigned int curL, curR;    // output cursors of the partition
     int shift;                  // compare (composite >> shift) with (prefix >> shift)
-    int done;
+    int done;                   // 0 selecting, 1 finished, 2 the unique candidate still has to be read back
+    // bracket select (large ranges): candidates are the elements with lowP <= composite <= highP
+    unsigned long long lowP, highP;
+    unsigned int cL;            // elements below lowP
+    unsigned int cand_cnt;      // candidates written to the candidate arrays (at the range's own slots)
+    int use_cand;               // 1: the digit passes run on the candidate arrays
+    int pad_;
 };
 
 struct Cols {
@@ -45,14 +51,17 @@ struct BuildScratch {
     unsigned* ghist;
     MaxRec* rec;
     int* err;
-    float* keybuf;  // gather mode only
+    float* keybuf;     // gather mode only
+    float* cand_key;   // bracket select: candidate keys (raw float bits) ...
+    int32_t* cand_idx; // ... and point indices, n entries each; null disables the bracket
+    unsigned* cand_cta; // candidates found by every CTA of k_bracket
 };
 
 struct BuildPlan {
     int64_t n;
     int dim, ncol, finish_level;
     int64_t max_seg, max_rec;
-    size_t off_col[2][kMaxCarry], off_idx[2], off_key, off_state, off_hist, off_rec, off_err, bytes;
+    size_t off_col[2][kMaxCarry], off_idx[2], off_key, off_state, off_hist, off_rec, off_err, off_ckey, off_cidx, off_ccta, bytes;
 };
 
 BuildPlan make_plan(int64_t n, int dim);

@@ -57,7 +57,7 @@ struct MaxSlot { unsigned long long comp; unsigned off; unsigned valid; };
 
 struct DistLayout {
     size_t ctl, flags, hist_slots, lhist, cnt_slots, max_slots, rec, col[2][kMaxCarry], idx[2], perm, tp;
-    size_t st, ghist, lrec, lerr;  // scratch of the local (single-GPU) phase
+    size_t st, ghist, lrec, lerr, ckey, cidx, ccta;  // scratch of the local (single-GPU) phase
     size_t bytes;
     int64_t cap, max_seg, max_rec;
 };
@@ -88,6 +88,9 @@ static DistLayout make_layout(int64_t n_total, int dim, int world, bool with_tp)
     L.ghist = take((size_t)L.max_seg * kDigitBins * 4);
     L.lrec = take((size_t)L.max_rec * sizeof(MaxRec));
     L.lerr = take(256);
+    L.ckey = take((size_t)L.cap * 4);
+    L.cidx = take((size_t)L.cap * 4);
+    L.ccta = take((size_t)L.max_rec * 4);
     L.bytes = off;
     return L;
 }
@@ -731,6 +734,9 @@ static int local_build(const HostCtx& H, cudaStream_t st) {
     sc.ghist = (unsigned*)(base + P.L.ghist);
     sc.rec = (MaxRec*)(base + P.L.lrec);
     sc.err = (int*)(base + P.L.lerr);
+    sc.cand_key = (float*)(base + P.L.ckey);
+    sc.cand_idx = (int32_t*)(base + P.L.cidx);
+    sc.cand_cta = (unsigned*)(base + P.L.ccta);
     if (cudaMemsetAsync(sc.ghist, 0, (size_t)P.L.max_seg * kDigitBins * 4, st) != cudaSuccess ||
         cudaMemsetAsync(sc.err, 0, 256, st) != cudaSuccess)
         return fail("kd_dist_local_build: cudaMemsetAsync failed");
