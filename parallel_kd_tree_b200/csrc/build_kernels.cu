@@ -152,14 +152,15 @@ __global__ void __launch_bounds__(BLOCK) k_bracket(const float* __restrict__ key
             const unsigned i = tb + k * BLOCK + tid;
             const unsigned key = ordered_key(f[k]);
             bool cand = false;
-            int id = 0;
             if (i < e) {
                 if (key < lowK) ++less;
-                else if (key <= highK) {  // the index is needed only inside (or on the edge of) the bracket
-                    id = idx[i];
-                    const unsigned long long c = composite(key, (unsigned)id);
-                    if (c < lowP) ++less;
-                    else cand = c <= highP;
+                else if (key <= highK) {
+                    cand = true;
+                    if (key == lowK || key == highK) {  // only on the bracket's edge keys does the index decide
+                        const unsigned long long c = composite(key, (unsigned)idx[i]);
+                        if (c < lowP) { ++less; cand = false; }
+                        else cand = c <= highP;
+                    }
                 }
             }
             const unsigned bc = __ballot_sync(0xffffffffu, cand);
@@ -170,7 +171,7 @@ __global__ void __launch_bounds__(BLOCK) k_bracket(const float* __restrict__ key
                 if (cand) {
                     const unsigned p = b + w + __popc(bc & ((1u << lane) - 1u));
                     cand_key[p] = f[k];
-                    cand_idx[p] = id;
+                    cand_idx[p] = (int32_t)i;  // the candidate's slot: its index is fetched only if a pass needs it
                 }
             }
         }
@@ -213,7 +214,8 @@ __global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys_a
     // the pinned last slot never takes part (kdtree_sequential.cpp:46-48); after a successful bracket the
     // passes run on the range's candidates instead of on all of its keys
     const float* __restrict__ keys = S.use_cand ? cand_key : keys_all;
-    const int32_t* __restrict__ idx = S.use_cand ? cand_idx : idx_all;
+    const bool via = S.use_cand != 0;  // candidates carry their slot; the point index is read through it
+    auto point_index = [&](unsigned i) -> unsigned { return (unsigned)(via ? idx_all[cand_idx[i]] : idx_all[i]); };
     const unsigned free_n = n - 1;
     const unsigned chunk = (free_n + cps - 1) / cps;
     const unsigned b = min(lo + j * chunk, lo + free_n);
@@ -224,8 +226,12 @@ __global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys_a
         // exactly one candidate matches the prefix, but elements outside the bracket may share those bits:
         // read the candidate back so that the partition compares complete composites
         const int psh = S.shift;
+        const int ksh = psh >= 32 ? psh - 32 : 0;
+        const unsigned wantk = (unsigned)(S.prefix >> 32) >> ksh;
         for (unsigned i = b + threadIdx.x; i < e; i += BLOCK) {
-            const unsigned long long c = composite(ordered_key(keys[i]), (unsigned)idx[i]);
+            const unsigned key = ordered_key(keys[i]);
+            if ((key >> ksh) != wantk) continue;  // the index is fetched only for keys that can match
+            const unsigned long long c = composite(key, point_index(i));
             if ((c >> psh) == (S.prefix >> psh)) {
                 st[s].prefix = c;
                 st[s].shift = 0;
@@ -270,7 +276,7 @@ __global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys_a
             for (int u = 0; u < UNROLL; ++u) {
                 unsigned i = i0 + u * BLOCK;
                 bool valid = i < e && ordered_key(f[u]) == wantkey;
-                unsigned id = valid ? (unsigned)idx[i] : 0u;
+                unsigned id = valid ? point_index(i) : 0u;
                 if (d > 3) valid = valid && ((id >> ps) == wantidx);
                 warp_hist_add(sh, (id >> dsh) & mask, valid);
             }
@@ -1107,7 +1113,7 @@ int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, u
         if (bracket) {
             k_sample<<<(unsigned)nseg, 512, 0, stream>>>(keys, buf[cur].idx, sc.st, N, level);
             KD_LAUNCH_CHECK("k_sample");
-            k_bracket<512, 4><<<(unsigned)(nseg * cps_p), 512, 0, stream>>>(keys, buf[cur].idx, sc.st, sc.cand_key,
+            k_bracket<512, 8><<<(unsigned)(nseg * cps_p), 512, 0, stream>>>(keys, buf[cur].idx, sc.st, sc.cand_key,
                                                                            sc.cand_idx, sc.cand_cta, N, level, cps_p);
             KD_LAUNCH_CHECK("k_bracket");
             k_bracket_finish<<<(unsigned)((nseg + 255) / 256), 256, 0, stream>>>(sc.st, N, level, (unsigned)nseg);
