@@ -1130,7 +1130,7 @@ int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, u
             KD_LAUNCH_CHECK("k_scan");
         }
         {
-            constexpr int PB = 512, PI = 4;
+            constexpr int PB = 128, PI = 4;
             const unsigned grid = (unsigned)(nseg * cps_p);
 #define KD_PART(NC)                                                                                                \
     k_partition<NC, PB, PI><<<grid, PB, 0, stream>>>(buf[cur], buf[cur ^ 1], keys, axis, sc.st, sc.rec, out, out_lo, \
