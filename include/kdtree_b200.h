@@ -83,6 +83,12 @@ int64_t kd_last_launch_count(void);
 int kd_nearest_gpu(const float* tree_points, const int32_t* perm, int64_t n, int dim, const float* queries,
                    int64_t nq, int32_t* out_index, float* out_dist2, float* out_dist, int32_t* out_visited,
                    void* stream);
+/* Batched k-NN (extension; the reference has k = 1): the reference traversal with a bounded sorted list of the k
+ * best nodes; outputs [nq][k] ascending, -1 / +inf padded; 1 <= k <= 32; k = 1 equals kd_nearest_*. */
+int kd_knn_cpu(const float* points, int64_t n, int dim, const int32_t* perm, const float* queries, int64_t nq, int k,
+               int32_t* out_index, float* out_dist2);
+int kd_knn_gpu(const float* tree_points, const int32_t* perm, int64_t n, int dim, const float* queries, int64_t nq,
+               int k, int32_t* out_index, float* out_dist2, void* stream);
 int kd_gather_rows_gpu(const float* points, const int32_t* perm, int64_t n, int dim, float* out, void* stream);
 int kd_materialize_nodes_gpu(int64_t n, const int32_t* perm, int32_t* node_point, int32_t* left, int32_t* right,
                              void* stream);

@@ -51,6 +51,8 @@ def _declare(lib):
         "kd_build_status": (i32, [vp, i64, i32, vp]),
         "kd_last_launch_count": (i64, []),
         "kd_nearest_gpu": (i32, [vp, vp, i64, i32, vp, i64, vp, vp, vp, vp, vp]),
+        "kd_knn_cpu": (i32, [vp, i64, i32, vp, vp, i64, i32, vp, vp]),
+        "kd_knn_gpu": (i32, [vp, vp, i64, i32, vp, i64, i32, vp, vp, vp]),
         "kd_gather_rows_gpu": (i32, [vp, vp, i64, i32, vp, vp]),
         "kd_materialize_nodes_gpu": (i32, [i64, vp, vp, vp, vp, vp]),
         "kd_bbox_gpu": (i32, [vp, i64, i32, vp, vp, vp]),

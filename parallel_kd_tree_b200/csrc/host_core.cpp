@@ -272,6 +272,58 @@ int kd_nearest_cpu(const float* points, int64_t n, int dim, const int32_t* perm,
     return 0;
 }
 
+int kd_knn_cpu(const float* points, int64_t n, int dim, const int32_t* perm, const float* queries, int64_t nq, int k,
+               int32_t* out_index, float* out_dist2) {
+    // k-NN extension: the reference traversal with a bounded sorted list (definition in query_kernels.cu)
+    if (!points || !perm || !queries || !out_index || !out_dist2 || n <= 0 || dim <= 0 || nq < 0 || k < 1 || k > 32)
+        return kd::fail("kd_knn_cpu: bad arguments (1 <= k <= 32)");
+    struct Far { int64_t lo, n; int depth; float da2; };
+    std::vector<Far> st;
+    std::vector<float> bd(k);
+    std::vector<int32_t> bp(k);
+    for (int64_t q = 0; q < nq; ++q) {
+        const float* qp = queries + (size_t)q * dim;
+        int have = 0;
+        int64_t lo = 0, cnt = n;
+        int depth = 0;
+        st.clear();
+        for (;;) {
+            while (cnt > 0) {
+                int64_t m = cnt / 2;
+                int32_t p = perm[lo + m];
+                const float* pp = points + (size_t)p * dim;
+                int axis = depth % dim;
+                float de = 0;
+                for (int i = 0; i < dim; ++i) { float t = pp[i] - qp[i]; de += t * t; }
+                float da = qp[axis] - pp[axis];
+                if (have < k || de < bd[have - 1]) {
+                    int at = have < k ? have : k - 1;
+                    while (at > 0 && bd[at - 1] > de) { bd[at] = bd[at - 1]; bp[at] = bp[at - 1]; --at; }
+                    bd[at] = de;
+                    bp[at] = p;
+                    if (have < k) ++have;
+                }
+                float da2 = da * da;
+                if (da < 0) { st.push_back({lo + m + 1, cnt - m - 1, depth + 1, da2}); cnt = m; }
+                else { st.push_back({lo, m, depth + 1, da2}); lo = lo + m + 1; cnt = cnt - m - 1; }
+                ++depth;
+            }
+            bool resumed = false;
+            while (!st.empty()) {
+                Far f = st.back();
+                st.pop_back();
+                if (f.n > 0 && (have < k || f.da2 < bd[have - 1])) { lo = f.lo; cnt = f.n; depth = f.depth; resumed = true; break; }
+            }
+            if (!resumed) break;
+        }
+        for (int i = 0; i < k; ++i) {
+            out_index[(size_t)q * k + i] = i < have ? bp[i] : -1;
+            out_dist2[(size_t)q * k + i] = i < have ? bd[i] : INFINITY;
+        }
+    }
+    return 0;
+}
+
 int64_t kd_root_slot(int64_t n) { return n > 0 ? n / 2 : -1; }
 
 int kd_materialize_nodes_cpu(int64_t n, const int32_t* perm, int32_t* node_point, int32_t* left, int32_t* right) {

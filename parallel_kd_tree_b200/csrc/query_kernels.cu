@@ -181,3 +181,80 @@ int kd_bbox_gpu(const float* points, int64_t n, int dim, float* out_min, float* 
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// Batched k-NN (extension: the reference answers k = 1 only).  Definition: the reference's traversal
+// (same visiting order, near side first) with a bounded list of the k best nodes seen so far instead of
+// one; a node enters the list iff the list is not full or its distance is strictly smaller than the
+// current k-th best; the far side is visited iff the list is not full or da*da < current k-th best.
+// For k = 1 this is exactly kdtree_sequential.cpp:75-136.  The list is kept sorted (ascending, earlier
+// visit first among equals); k <= kMaxK.  kd_knn_cpu (host_core.cpp) is the same definition on the host.
+// ------------------------------------------------------------------------------------------------
+namespace kd {
+constexpr int kMaxK = 32;
+
+__global__ void __launch_bounds__(128) k_knn(const float* __restrict__ tp, const int32_t* __restrict__ perm, unsigned N,
+                                             int dim, const float* __restrict__ queries, long long nq, int k,
+                                             int32_t* __restrict__ out_index, float* __restrict__ out_d2) {
+    long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    const float* qp = queries + (size_t)q * dim;
+    unsigned st_lo[kMaxDepth], st_n[kMaxDepth];
+    float st_da2[kMaxDepth];
+    unsigned char st_depth[kMaxDepth];
+    float bd[kMaxK];
+    unsigned bs[kMaxK];
+    int have = 0, sp = 0;
+    unsigned lo = 0, cnt = N;
+    int depth = 0;
+    for (;;) {
+        while (cnt > 0) {
+            unsigned m = cnt >> 1, slot = lo + m;
+            const float* pp = tp + (size_t)slot * dim;
+            int axis = depth % dim;
+            float de = dist2_exact(pp, qp, dim);
+            float da = __fsub_rn(qp[axis], pp[axis]);
+            if (have < k || de < bd[have - 1]) {
+                int p = have < k ? have : k - 1;        // insertion, stable for equal distances
+                while (p > 0 && bd[p - 1] > de) { bd[p] = bd[p - 1]; bs[p] = bs[p - 1]; --p; }
+                bd[p] = de;
+                bs[p] = slot;
+                if (have < k) ++have;
+            }
+            unsigned rlo = slot + 1, rn = cnt - m - 1;
+            st_da2[sp] = __fmul_rn(da, da);
+            st_depth[sp] = (unsigned char)(depth + 1);
+            if (da < 0.f) { st_lo[sp] = rlo; st_n[sp] = rn; cnt = m; }
+            else { st_lo[sp] = lo; st_n[sp] = m; lo = rlo; cnt = rn; }
+            ++sp;
+            ++depth;
+        }
+        bool resumed = false;
+        while (sp > 0) {
+            --sp;
+            if (st_n[sp] > 0 && (have < k || st_da2[sp] < bd[have - 1])) {
+                lo = st_lo[sp]; cnt = st_n[sp]; depth = st_depth[sp];
+                resumed = true;
+                break;
+            }
+        }
+        if (!resumed) break;
+    }
+    for (int i = 0; i < k; ++i) {
+        out_index[(size_t)q * k + i] = i < have ? perm[bs[i]] : -1;
+        out_d2[(size_t)q * k + i] = i < have ? bd[i] : __int_as_float(0x7f800000);
+    }
+}
+}  // namespace kd
+
+extern "C" int kd_knn_gpu(const float* tree_points, const int32_t* perm, int64_t n, int dim, const float* queries,
+                          int64_t nq, int k, int32_t* out_index, float* out_dist2, void* stream) {
+    if (!tree_points || !perm || !queries || !out_index || !out_dist2 || n <= 0 || dim <= 0 || nq < 0 || k < 1 ||
+        k > kd::kMaxK || n >= (1ll << 31))
+        return kd::fail("kd_knn_gpu: bad arguments (1 <= k <= 32)");
+    if (nq == 0) return 0;
+    kd::k_knn<<<(unsigned)((nq + 127) / 128), 128, 0, (cudaStream_t)stream>>>(tree_points, perm, (unsigned)n, dim, queries,
+                                                                             nq, k, out_index, out_dist2);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : kd::fail(std::string("kd_knn_gpu: ") + cudaGetErrorString(e));
+}

@@ -69,6 +69,15 @@ class KDTree:
         idx, d2, d, vis = ops.nearest(self.tree_points, self.perm, queries)
         return NNResult(index=idx, ids=idx + (1 + self.id_offset), dist2=d2, dist=d, visited=vis)
 
+    def knn(self, queries: torch.Tensor, k: int):
+        """k nearest nodes per query by the reference traversal with a k-best list: (ids [nq, k], dist [nq, k])."""
+        queries = queries.to(self.device, torch.float32)
+        if queries.dim() == 1:
+            queries = queries[None]
+        idx, d2 = ops.knn(self.tree_points, self.perm, queries, k)
+        ids = torch.where(idx >= 0, idx + (1 + self.id_offset), idx)
+        return ids, d2.sqrt()
+
     # -- structure -------------------------------------------------------------------------
     def nodes(self):
         """(node_point, left, right) int32 arrays indexed by slot, -1 = nullptr (Node.hpp:35-45)."""

@@ -110,3 +110,31 @@ def _(points):
 def bbox(points: torch.Tensor):
     """Per-axis (min, max) of a point set."""
     return torch.ops.kd.bbox(points)
+
+
+def knn(tree_points: torch.Tensor, perm: torch.Tensor, queries: torch.Tensor, k: int):
+    """Batched k-NN (extension: the reference has k = 1): (point index [nq, k], dist² [nq, k]), ascending.
+
+    Same traversal as ``nearest`` with a bounded list of the k best nodes; ``k = 1`` gives the reference's answers.
+    """
+    tree_points = as_points(tree_points, "tree_points")
+    queries = as_points(queries, "queries")
+    n, dim = tree_points.shape
+    if queries.shape[1] != dim:
+        raise ValueError("Dimensions do not match!")
+    nq = queries.shape[0]
+    dev = tree_points.device
+    perm = perm.to(torch.int32).contiguous()
+    idx = torch.empty((nq, k), dtype=torch.int32, device=dev)
+    d2 = torch.empty((nq, k), dtype=torch.float32, device=dev)
+    if tree_points.is_cuda:
+        with torch.cuda.device(dev):
+            check(lib().kd_knn_gpu(tree_points.data_ptr(), perm.data_ptr(), n, dim, queries.data_ptr(), nq, int(k),
+                                   idx.data_ptr(), d2.data_ptr(), stream_ptr(dev)), "kd::knn")
+    else:
+        ident = torch.arange(n, dtype=torch.int32)
+        slot = torch.empty((nq, k), dtype=torch.int32)
+        check(lib().kd_knn_cpu(tree_points.data_ptr(), n, dim, ident.data_ptr(), queries.data_ptr(), nq, int(k),
+                               slot.data_ptr(), d2.data_ptr()), "kd::knn")
+        idx = torch.where(slot >= 0, perm[slot.clamp(min=0).long()], slot)
+    return idx, d2

@@ -46,3 +46,13 @@ def test_forest_on_gpu_matches_cpu_forest(kd):
     dc, ic = forest_c.nearest(qs)
     dg, ig = forest_g.nearest(qs)
     assert torch.equal(dc, dg) and torch.equal(ic, ig)
+
+
+@pytest.mark.parametrize("dim,n,nq,k", [(3, 50000, 500, 1), (3, 50000, 500, 8), (8, 100000, 300, 16), (2, 3, 10, 5)])
+def test_knn_gpu_equals_cpu_definition(kd, dim, n, nq, k):
+    pts, qs = kd.ops.generate_problem(4, dim, n, nq)
+    tc, tg = kd.KDTree(pts), kd.KDTree(pts.cuda())
+    ic, dc = kd.ops.knn(tc.tree_points, tc.perm, qs, k)            # squared distances: exact on both sides
+    ig, dg = kd.ops.knn(tg.tree_points, tg.perm, qs.cuda(), k)
+    assert torch.equal(ig.cpu(), ic)
+    assert torch.equal(dg.cpu().view(torch.int32), dc.view(torch.int32))

@@ -119,3 +119,22 @@ def test_state_dict_roundtrip(kd):
     again = kd.KDTree.from_state_dict(tree.state_dict())
     assert torch.equal(again.perm, tree.perm)
     assert torch.equal(again.nearest(qs).dist, tree.nearest(qs).dist)
+
+
+def test_knn_extension_cpu(kd):
+    # k = 1 is the reference's 1-NN; for k > 1 every list is ascending and, in 1-D (where the reference's
+    # trees are valid kd-trees, SURVEY.md §0: 0 % wrong answers), equals brute force
+    pts, qs = kd.ops.generate_problem(3, 3, 5000, 40)
+    tree = kd.KDTree(pts)
+    ids1, d1 = tree.knn(qs, 1)
+    ref = tree.nearest(qs)
+    assert torch.equal(ids1[:, 0], ref.ids) and torch.equal(d1[:, 0], ref.dist)
+    ids, d = tree.knn(qs, 8)
+    assert bool((d[:, 1:] >= d[:, :-1]).all())
+    pts, qs = kd.ops.generate_problem(5, 1, 3000, 25)
+    tree = kd.KDTree(pts)
+    ids, d = tree.knn(qs, 5)
+    brute = torch.cdist(qs.double(), pts.double()).topk(5, largest=False)
+    assert torch.equal(ids.long() - 1, brute.indices)
+    ids, d = kd.KDTree(pts[:3]).knn(qs, 5)
+    assert (ids[:, 3:] == -1).all() and torch.isinf(d[:, 3:]).all()
