@@ -105,6 +105,7 @@ typedef struct {
     int world, rank, dim, with_tree_points;
     int64_t n_total;
     void* heap[8];
+    void* mc_heap; /* optional NVLS multicast mapping of the same heaps (one store reaches every GPU); NULL = none */
 } kd_dist_ctx;
 size_t kd_dist_heap_bytes(int64_t n_total, int dim, int world, int with_tree_points);
 int kd_dist_offsets(int64_t n_total, int dim, int world, int with_tree_points, size_t* perm_off, size_t* tp_off);

@@ -22,7 +22,7 @@ class KdError(RuntimeError):
 class DistCtx(C.Structure):
     """kd_dist_ctx of include/kdtree_b200.h"""
     _fields_ = [("world", C.c_int), ("rank", C.c_int), ("dim", C.c_int), ("with_tree_points", C.c_int),
-                ("n_total", C.c_int64), ("heap", C.c_void_p * 8)]
+                ("n_total", C.c_int64), ("heap", C.c_void_p * 8), ("mc_heap", C.c_void_p)]
 
 
 def _declare(lib):

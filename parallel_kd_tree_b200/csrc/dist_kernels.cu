@@ -99,6 +99,7 @@ struct DistParams {
     int world, rank, dim, ncol;
     unsigned N;
     unsigned char* heap[kMaxWorld];  // this rank's view of every rank's heap
+    unsigned char* mc;               // NVLS multicast view of the heaps (a store lands on every GPU) or null
     DistLayout L;
 };
 
@@ -494,10 +495,14 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
     }
     if (has_node) {
         // the node of this range: slot lo + n/2 of every GPU's tree arrays
-        for (int r = 0; r < P.world; ++r) {
-            reinterpret_cast<int32_t*>(P.heap[r] + P.L.perm)[g.lo + m] = node_id;
+        // (with an NVLS multicast mapping one store is replicated by the switch: multimem.st lowers to a plain
+        // STG on the multicast address, so the same code path serves both)
+        const int nrep = P.mc ? 1 : P.world;
+        for (int r = 0; r < nrep; ++r) {
+            unsigned char* base = P.mc ? P.mc : P.heap[r];
+            reinterpret_cast<int32_t*>(base + P.L.perm)[g.lo + m] = node_id;
             if (with_tp) {
-                float* tp = reinterpret_cast<float*>(P.heap[r] + P.L.tp);
+                float* tp = reinterpret_cast<float*>(base + P.L.tp);
 #pragma unroll
                 for (int c = 0; c < NCOL; ++c) tp[(size_t)(g.lo + m) * P.dim + c] = node_val[c];
             }
@@ -741,10 +746,16 @@ static int local_build(const HostCtx& H, cudaStream_t st) {
         cudaMemsetAsync(sc.err, 0, 256, st) != cudaSuccess)
         return fail("kd_dist_local_build: cudaMemsetAsync failed");
     OutPtrs out{};
-    out.n = P.world;
-    for (int r = 0; r < P.world; ++r) {
-        out.perm[r] = (int32_t*)(P.heap[r] + P.L.perm);
-        out.tp[r] = H.with_tp ? (float*)(P.heap[r] + P.L.tp) : nullptr;
+    if (P.mc) {  // one replica: the multicast mapping, the switch fans the stores out to every GPU
+        out.n = 1;
+        out.perm[0] = (int32_t*)(P.mc + P.L.perm);
+        out.tp[0] = H.with_tp ? (float*)(P.mc + P.L.tp) : nullptr;
+    } else {
+        out.n = P.world;
+        for (int r = 0; r < P.world; ++r) {
+            out.perm[r] = (int32_t*)(P.heap[r] + P.L.perm);
+            out.tp[r] = H.with_tp ? (float*)(P.heap[r] + P.L.tp) : nullptr;
+        }
     }
     return build_core(buf, L & 1, (int64_t)n, P.dim, P.ncol, L, lo, out, nullptr, sc, st);
 }
@@ -771,6 +782,7 @@ static int fill_ctx(const kd_dist_ctx* c, kd::HostCtx& H) {
     H.with_tp = c->with_tree_points != 0;
     H.P.L = kd::make_layout(c->n_total, c->dim, c->world, H.with_tp);
     for (int r = 0; r < kd::kMaxWorld; ++r) H.P.heap[r] = r < c->world ? (unsigned char*)c->heap[r] : nullptr;
+    H.P.mc = (unsigned char*)c->mc_heap;
     for (int r = 0; r < c->world; ++r)
         if (!H.P.heap[r]) return kd::fail("kd_dist: missing heap pointer");
     return 0;

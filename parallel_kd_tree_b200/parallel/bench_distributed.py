@@ -88,7 +88,9 @@ def run(args, kd, dist, rank, world, dev, sampler_cls, baseline_pps):
                                   "no NCCL on the data path)",
                    "l2": "inputs and working set exceed the 126 MB L2; no flush needed",
                    "baseline": "BASELINE.md row 15: reference forest W=8 build, 4.2e5 points/s",
-                   "replicas_consistent": consistent, "host_generate_s": round(gen_s, 2)},
+                   "replicas_consistent": consistent,
+                   "heap": "torch symmetric memory + NVLS multicast stores for the tree arrays" if db.multicast
+                   else ("torch symmetric memory, unicast P2P stores" if db._symm is not None else "cudaMalloc + CUDA IPC, unicast P2P stores"), "host_generate_s": round(gen_s, 2)},
         "clocks": clocks,
         "e2e": {"value": n / e2e_s, "unit": "points/s", "ms_per_step": e2e_s * 1e3,
                 "h2d_bytes_per_step": host_local.numel() * 4 * world, "d2h_bytes_per_step": n * 4},

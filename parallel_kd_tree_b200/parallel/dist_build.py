@@ -56,8 +56,9 @@ class _Base:
         self.perm_off, self.tp_off = _offsets(self.n_total, self.dim, self.world, self.with_tp)
         self.serial = 0
 
-    def _ctx(self, rank: int, heap_ptrs) -> DistCtx:
+    def _ctx(self, rank: int, heap_ptrs, mc_ptr=None) -> DistCtx:
         c = DistCtx()
+        c.mc_heap = mc_ptr
         c.world, c.rank, c.dim, c.with_tree_points, c.n_total = self.world, rank, self.dim, int(self.with_tp), self.n_total
         for r in range(8):
             c.heap[r] = heap_ptrs[r] if r < self.world else None
@@ -120,20 +121,54 @@ class EmulatedDistBuild(_Base):
 class IpcDistBuild(_Base):
     """One process per GPU; heaps are mapped into every peer with CUDA IPC."""
 
-    def __init__(self, n_total, dim, group=None, with_tree_points=True):
+    def __init__(self, n_total, dim, group=None, with_tree_points=True, backend="auto"):
+        """``backend``: "symm" = torch symmetric memory (gives an NVLS multicast mapping when the fabric has one),
+        "ipc" = cudaMalloc + CUDA IPC handles, "auto" = symm if it works, else ipc."""
+        import os
+
         import torch.distributed as dist
+        backend = os.environ.get("KD_DIST_BACKEND", backend)
         self.group = group
         self.rank = dist.get_rank(group)
         world = dist.get_world_size(group)
         super().__init__(n_total, dim, world, with_tree_points)
         self.device = torch.device("cuda", torch.cuda.current_device())
+        self._own, self._peers, self._symm = None, [], None
+        self.multicast = False
+        if backend in ("auto", "symm"):
+            try:
+                self._init_symm(dist, group)
+            except Exception:
+                if backend == "symm":
+                    raise
+                self._symm = None
+        if self._symm is None:
+            self._init_ipc(dist, group)
+        self.perm, self.tree_points = self._views(self.heap)
+        dist.barrier(group=group)      # every heap is mapped (and zeroed) before anybody posts a flag
+
+    def _init_symm(self, dist, group):
+        import torch.distributed._symmetric_memory as symm_mem
+        g = group if group is not None else dist.group.WORLD
+        heap = symm_mem.empty(self.heap_bytes, dtype=torch.uint8, device=self.device)
+        heap.zero_()
+        torch.cuda.synchronize(self.device)
+        hdl = symm_mem.rendezvous(heap, g.group_name)
+        ptrs = [int(p) for p in hdl.buffer_ptrs]
+        mc = int(hdl.multicast_ptr) if getattr(hdl, "multicast_ptr", 0) else None
+        self._symm, self.heap = hdl, heap
+        self.multicast = mc is not None
+        self.ctx = self._ctx(self.rank, ptrs, mc)
+
+    def _init_ipc(self, dist, group):
         L = lib()
+        world = self.world
         ptr, handle = C.c_void_p(), C.create_string_buffer(64)
         check(L.kd_symm_alloc(self.heap_bytes, C.byref(ptr), handle), "kd_symm_alloc")
         self._own = ptr.value
         handles = [None] * world
         dist.all_gather_object(handles, bytes(handle.raw), group=group)   # bootstrap only
-        self._peers, ptrs = [], []
+        ptrs = []
         for r in range(world):
             if r == self.rank:
                 ptrs.append(self._own)
@@ -144,8 +179,6 @@ class IpcDistBuild(_Base):
             ptrs.append(p.value)
         self.ctx = self._ctx(self.rank, ptrs)
         self.heap = torch.as_tensor(_RawCuda(self._own, self.heap_bytes), device=self.device)
-        self.perm, self.tree_points = self._views(self.heap)
-        dist.barrier(group=group)      # every heap is mapped (and zeroed) before anybody posts a flag
 
     def slice(self):
         return slice_bounds(self.n_total, self.world, self.rank)

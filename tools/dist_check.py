@@ -21,6 +21,8 @@ for spec in (sys.argv[1:] or ["100003x3", "1048576x2", "4194304x3"]):
     first, local = kd.models.slice_bounds(n, world, rank)
     pts = kd.ops.generate_uniform(5, dim, n)
     db = IpcDistBuild(n, dim)
+    if rank == 0:
+        print(f"heap backend: symm={db._symm is not None} multicast={db.multicast}", flush=True)
     for trial in range(2):
         perm, tp = db.build(pts[first:first + local])
         db.status()
