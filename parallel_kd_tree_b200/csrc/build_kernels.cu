@@ -32,11 +32,24 @@ namespace kd {
 // ------------------------------------------------------------------------------------------
 // K1: working columns
 // ------------------------------------------------------------------------------------------
-__global__ void k_init(const float* __restrict__ pts, unsigned N, int dim, int ncol, Cols dst) {
-    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= N) return;
-    dst.idx[i] = (int32_t)i;
-    for (int c = 0; c < ncol; ++c) dst.c[c][i] = pts[(size_t)i * dim + c];
+// AoS rows -> SoA columns through a shared-memory tile: the rows are read as one flat coalesced run and
+// every column is written as a coalesced run (a thread-per-row version touches each 128-byte line `dim` times)
+constexpr int kInitRows = 1024, kInitBlock = 256;
+__global__ void __launch_bounds__(kInitBlock) k_init(const float* __restrict__ pts, unsigned N, int dim, int ncol,
+                                                     Cols dst) {
+    __shared__ float tile[kInitRows * kMaxCarry];
+    const unsigned row0 = blockIdx.x * kInitRows, tid = threadIdx.x;
+    const unsigned rows = min((unsigned)kInitRows, N - row0);
+    for (unsigned r = tid; r < rows; r += kInitBlock) dst.idx[row0 + r] = (int32_t)(row0 + r);
+    if (ncol == 0) return;
+    const unsigned total = rows * (unsigned)dim;
+    const float* __restrict__ src = pts + (size_t)row0 * dim;
+#pragma unroll 4
+    for (unsigned e = tid; e < total; e += kInitBlock) tile[e] = src[e];
+    __syncthreads();
+    for (int c = 0; c < ncol; ++c)
+#pragma unroll 4
+        for (unsigned r = tid; r < rows; r += kInitBlock) dst.c[c][row0 + r] = tile[r * dim + c];
 }
 
 __global__ void k_state_init(SegState* st, unsigned N, int level, unsigned nseg) {
@@ -1185,7 +1198,7 @@ int build_gpu(const float* points, int64_t n, int dim, int32_t* perm, float* tre
     if (cudaMemsetAsync(sc.ghist, 0, (size_t)p.max_seg * kDigitBins * 4, stream) != cudaSuccess ||
         cudaMemsetAsync(sc.err, 0, 256, stream) != cudaSuccess)
         return fail("kd_build_gpu: cudaMemsetAsync failed");
-    k_init<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(points, N, dim, p.ncol, buf[0]);
+    k_init<<<(unsigned)((n + kInitRows - 1) / kInitRows), kInitBlock, 0, stream>>>(points, N, dim, p.ncol, buf[0]);
     KD_LAUNCH_CHECK("k_init");
     OutPtrs out{};
     out.n = 1;
