@@ -480,17 +480,38 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
             }
         }
         __syncthreads();
-        // ... and push it out as two contiguous runs: consecutive threads -> consecutive remote slots, so a warp
-        // store is one whole 128-byte line on the owner GPU (owner changes at most a few times per run)
-        for (unsigned t = tid; t < nl + nrt; t += BLOCK) {
-            const bool left = t < nl;
-            const unsigned o = left ? baseL + t : baseR + (t - nl);
-            unsigned mem, pos;
-            owner_of(o, left ? m : nr, Gh, mem, pos);
-            const Cols& d = dst[left ? mem : Gh + mem];
+        // ... and push it out as contiguous runs with 16-byte stores (a run = the part of the left or right
+        // output that lands on one owner GPU; there are at most a few per tile): a warp then emits 512
+        // contiguous bytes per store instruction, which is what the NVLink egress path wants
+        for (int side_i = 0; side_i < 2; ++side_i) {
+            const unsigned cnt = side_i ? nrt : nl, s_first = side_i ? nl : 0u;
+            const unsigned n_c = side_i ? nr : m;
+            unsigned done = 0;
+            while (done < cnt) {
+                const unsigned o = (side_i ? baseR : baseL) + done;
+                unsigned mem, pos;
+                owner_of(o, n_c, Gh, mem, pos);
+                const unsigned room = share_of(n_c, Gh, mem) - pos;   // slots left on this owner
+                const unsigned k = min(cnt - done, room);
+                const Cols& d = dst[side_i ? Gh + mem : mem];
+                const unsigned s0 = s_first + done;
+                const unsigned head = min(k, (4u - (pos & 3u)) & 3u);  // elements before the first 16-byte boundary
+                const unsigned body = (k - head) >> 2;                 // whole 16-byte chunks
+                const unsigned tail0 = head + (body << 2);
 #pragma unroll
-            for (int c = 0; c < NCOL; ++c) d.c[c][pos] = stage[c * (BLOCK * IPT) + t];
-            d.idx[pos] = stage_idx[t];
+                for (int c = 0; c <= NCOL; ++c) {
+                    const float* __restrict__ sc = c < NCOL ? stage + (size_t)c * (BLOCK * IPT) + s0
+                                                           : reinterpret_cast<const float*>(stage_idx) + s0;
+                    float* __restrict__ dc = (c < NCOL ? d.c[c < NCOL ? c : 0] : reinterpret_cast<float*>(d.idx)) + pos;
+                    if ((unsigned)tid < head) dc[tid] = sc[tid];
+                    for (unsigned q = tid; q < body; q += BLOCK) {
+                        const unsigned e0 = head + (q << 2);
+                        *reinterpret_cast<float4*>(dc + e0) = make_float4(sc[e0], sc[e0 + 1], sc[e0 + 2], sc[e0 + 3]);
+                    }
+                    if (tail0 + tid < k) dc[tail0 + tid] = sc[tail0 + tid];
+                }
+                done += k;
+            }
         }
     }
     if (has_node) {
