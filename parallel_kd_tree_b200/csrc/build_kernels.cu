@@ -133,8 +133,10 @@ __global__ void __launch_bounds__(512) k_sample(const float* __restrict__ keys, 
 }
 
 // One streaming pass, no block-wide synchronisation: every CTA compacts the candidates of its chunk to the
-// chunk's own first slots of the candidate arrays (they can never overflow it) with warp-aggregated
-// shared-memory cursors, and publishes its count; the digit passes then visit (chunk start, count) per CTA.
+// chunk's own first slots of the candidate arrays (they can never overflow it) and publishes its count; the
+// digit passes then visit (chunk start, count) per CTA.  The pass is issue-bound, so the per-element work is
+// two float compares (float order == key order, -0 == +0 included); candidate slots are handed out once per
+// tile with a warp scan and one shared-memory atomic per warp.
 template <int BLOCK, int IPT>
 __global__ void __launch_bounds__(BLOCK) k_bracket(const float* __restrict__ keys, const int32_t* __restrict__ idx,
                                                    SegState* st, float* __restrict__ cand_key,
@@ -145,6 +147,10 @@ __global__ void __launch_bounds__(BLOCK) k_bracket(const float* __restrict__ key
     const int tid = threadIdx.x, lane = tid & 31;
     const unsigned long long lowP = st[s].lowP, highP = st[s].highP;
     const unsigned lowK = (unsigned)(lowP >> 32), highK = (unsigned)(highP >> 32);
+    auto key_float = [](unsigned k) { return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k); };
+    // an open end of the bracket (only for ranks near the ends of a range) becomes an infinite pivot
+    const float lowF = lowP == 0ull ? __int_as_float(0xff800000) : key_float(lowK);
+    const float highF = highP == ~0ull ? __int_as_float(0x7f800000) : key_float(highK);
     unsigned lo, n;
     seg_range(N, level, s, lo, n);
     const unsigned free_n = n - 1;
@@ -158,36 +164,44 @@ __global__ void __launch_bounds__(BLOCK) k_bracket(const float* __restrict__ key
 #pragma unroll
         for (int k = 0; k < IPT; ++k) {
             const unsigned i = tb + k * BLOCK + tid;
-            f[k] = i < e ? keys[i] : 0.f;
+            f[k] = i < e ? keys[i] : __int_as_float(0x7fc00000);  // NaN: neither below nor inside the bracket
         }
+        unsigned cmask = 0;
 #pragma unroll
         for (int k = 0; k < IPT; ++k) {
-            const unsigned i = tb + k * BLOCK + tid;
-            const unsigned key = ordered_key(f[k]);
-            bool cand = false;
-            if (i < e) {
-                if (key < lowK) ++less;
-                else if (key <= highK) {
-                    cand = true;
-                    if (key == lowK || key == highK) {  // only on the bracket's edge keys does the index decide
-                        const unsigned long long c = composite(key, (unsigned)idx[i]);
-                        if (c < lowP) { ++less; cand = false; }
-                        else cand = c <= highP;
-                    }
+            const float v = f[k];
+            if (v < lowF) ++less;
+            else if (v <= highF) {
+                bool cand = true;
+                if (v == lowF || v == highF) {  // only on the bracket's edge keys does the index decide
+                    const unsigned i = tb + k * BLOCK + tid;
+                    const unsigned long long c = composite(ordered_key(v), (unsigned)idx[i]);
+                    if (c < lowP) { ++less; cand = false; }
+                    else cand = c <= highP;
                 }
-            }
-            const unsigned bc = __ballot_sync(0xffffffffu, cand);
-            if (bc) {
-                unsigned w = 0;
-                if (lane == 0) w = atomicAdd(&s_cur, __popc(bc));
-                w = __shfl_sync(0xffffffffu, w, 0);
-                if (cand) {
-                    const unsigned p = b + w + __popc(bc & ((1u << lane) - 1u));
-                    cand_key[p] = f[k];
-                    cand_idx[p] = (int32_t)i;  // the candidate's slot: its index is fetched only if a pass needs it
-                }
+                cmask |= cand ? (1u << k) : 0u;
             }
         }
+        // candidate slots: exclusive warp scan of the per-thread counts, one shared atomic per warp
+        const unsigned mine = __popc(cmask);
+        unsigned inc = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        const unsigned total = __shfl_sync(0xffffffffu, inc, 31);
+        unsigned base = 0;
+        if (lane == 31 && total) base = atomicAdd(&s_cur, total);
+        base = __shfl_sync(0xffffffffu, base, 31);
+        unsigned p = b + base + inc - mine;
+#pragma unroll
+        for (int k = 0; k < IPT; ++k)
+            if (cmask & (1u << k)) {
+                cand_key[p] = f[k];
+                cand_idx[p] = (int32_t)(tb + k * BLOCK + tid);  // the candidate's slot; its index is fetched on demand
+                ++p;
+            }
     }
     for (int o = 16; o > 0; o >>= 1) less += __shfl_xor_sync(0xffffffffu, less, o);
     if (lane == 0 && less) atomicAdd(&s_less, less);
