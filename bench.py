@@ -11,7 +11,8 @@ far larger than the 126 MB L2, so no explicit L2 flush is needed between steps.
 
 `value` is device time (CUDA events, max over ranks); `e2e` repeats the measurement through the public
 API with, per step, the host->device copy of the points from pinned memory and the device->host copy
-of the finished tree (perm) inside the timed region.
+of the finished tree (perm) inside the timed region (wall clock; consecutive steps are pipelined on
+copy streams with double buffers, every byte still moves every step).
 """
 from __future__ import annotations
 

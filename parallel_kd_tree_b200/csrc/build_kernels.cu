@@ -9,10 +9,13 @@
 // old pinned element form the right range.  How it is built is new: a
 // level-synchronous select + partition, no sort, no recursion.
 //
-//   K1  k_init / k_gather_keys   SoA working columns (+ per-level key gather for dim > kMaxCarry)
-//   K2  k_hist + k_scan          segmented MSB radix select on the 64-bit composite (key, index)
-//   K3  k_partition + k_fixup    unstable three-way partition, node emission, left-max -> last slot
-//   K4  k_finish                 whole sub-tree of a <= kFinishT-point range inside shared memory
+//   K1  k_init / k_gather_keys          SoA working columns (+ per-level key gather for dim > kMaxCarry)
+//   K2  k_sample + k_bracket            large ranges: a sorted sample brackets the rank, one pass compacts the
+//       k_hist + k_scan                 ~10 % candidates, MSB radix select on the composite (key, index) over them
+//   K3  k_partition + k_fixup           large ranges: unstable three-way partition, node emission, left-max -> last slot
+//   K2+K3  k_medium                     ranges of 513..16384 points: one CTA selects and partitions in one kernel
+//   K4  k_finish                        windows of <= kFinishT slots: whole sub-trees inside shared memory
+//                                       (TMA-staged, register/shuffle bitonic networks)
 //
 // Ranges are never stored: range s of level l is found by walking the shape
 // rule (left n/2, right n-n/2-1) along the bits of s.

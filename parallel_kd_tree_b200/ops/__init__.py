@@ -4,8 +4,8 @@ Every operator is registered as a ``torch.library`` custom op in the ``kd``
 namespace (``torch.ops.kd.build`` ...) and dispatches on the device of its
 inputs: CUDA tensors run the hand-written sm_100a kernels of
 ``libkdtree_b200.so``, CPU tensors run the native C++ host core of the same
-library.  There is no PyTorch-eager fallback: if the library is missing the op
-raises.
+library (a few trivial CPU helpers — bbox, row gather — use plain torch).  CUDA
+inputs never fall back to PyTorch eager code: if the library is missing the op raises.
 
 Reference parity: ``generate_uniform`` = Utility.cpp:6-18 / kdtree_mpi.cpp:19-41,
 ``build`` = kdtree_sequential.cpp:30-70, ``nearest`` = kdtree_sequential.cpp:75-136,
