@@ -553,56 +553,72 @@ template <int NCOL, int DBITS>
 __global__ void __launch_bounds__(512, (NCOL <= 4 ? 3 : 1)) k_medium(Cols src, Cols dst, const float* __restrict__ keys, int axis,
                                                 OutPtrs out, unsigned out_lo, int dim, unsigned N, int level,
                                                 unsigned cap, int* err) {
-    // digit schedule over the 64-bit composite: 11/11/10 + 11/11/10 bits (as in k_hist) for the larger
-    // ranges, 8 x 8 bits for the small ones (a 256-bin histogram is cheaper to clear and scan than the
-    // few extra passes over keys that already sit in shared memory)
+    // Digits of DBITS bits (11 for the larger ranges, 8 below 4096 points: a 256-bin histogram is cheaper to
+    // clear and scan than the few extra passes over keys that already sit in shared memory).  The digits do
+    // not start at bit 63: the range's smallest and largest key are found while the keys are staged, the bits
+    // they share are the initial prefix, and the first digit sits right below them, so the first pass already
+    // splits the range into up to 2^DBITS bins.
     constexpr int kBins = 1 << DBITS;
-    constexpr int kPasses = DBITS == 8 ? 8 : kNumDigits;
-    auto dshift = [](int d) { return DBITS == 8 ? 56 - 8 * d : digit_shift(d); };
-    auto dbits = [](int d) { return DBITS == 8 ? 8 : digit_bits(d); };
     extern __shared__ __align__(16) unsigned char msm[];
     unsigned* skey = reinterpret_cast<unsigned*>(msm);   // [cap] ordered keys of the unpinned elements
     unsigned* hist = skey + cap;                         // [kBins]
     __shared__ unsigned s_w[16];
-    __shared__ unsigned long long s_prefix, s_best;
-    __shared__ unsigned s_rank, s_cnt, s_done, s_cur[2], s_kmax, s_cum;
+    __shared__ unsigned long long s_prefix, s_bcomp[16];
+    __shared__ unsigned s_rank, s_cnt, s_done, s_cur[2], s_cum, s_min, s_max, s_bpos[16];
     __shared__ int s_shift, s_bin;
     const unsigned tid = threadIdx.x, B = blockDim.x, lane = tid & 31, wid = tid >> 5;
     unsigned lo, n;
     seg_range(N, level, blockIdx.x, lo, n);
     const unsigned m = n >> 1, free_n = n - 1;
     const float* __restrict__ kcol = NCOL > 0 ? src.c[axis] : keys;
+    if (tid == 0) { s_rank = m; s_done = 0; s_shift = 64; s_cur[0] = s_cur[1] = 0; s_min = 0xffffffffu; s_max = 0u; }
+    __syncthreads();
+    unsigned kmin = 0xffffffffu, kmax = 0u;
     for (unsigned i0 = tid; i0 < free_n; i0 += 4 * B) {  // four loads in flight per thread
         float f[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) f[u] = (i0 + u * B) < free_n ? kcol[lo + i0 + u * B] : 0.f;
 #pragma unroll
         for (int u = 0; u < 4; ++u)
-            if ((i0 + u * B) < free_n) skey[i0 + u * B] = ordered_key(f[u]);
+            if ((i0 + u * B) < free_n) {
+                const unsigned key = ordered_key(f[u]);
+                skey[i0 + u * B] = key;
+                kmin = min(kmin, key);
+                kmax = max(kmax, key);
+            }
     }
-    if (tid == 0) { s_prefix = 0ull; s_rank = m; s_done = 0; s_shift = 64; s_cur[0] = s_cur[1] = 0; s_kmax = 0; s_best = 0ull; }
+    for (int o = 16; o > 0; o >>= 1) {
+        kmin = min(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
+        kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
+    }
+    if (lane == 0) { atomicMin(&s_min, kmin); atomicMax(&s_max, kmax); }
+    __syncthreads();
+    const unsigned vary = s_min ^ s_max;
+    const int top = vary ? 32 - __clz(vary) : 0;  // the low `top` key bits differ inside the range
+    if (tid == 0) s_prefix = top >= 32 ? 0ull : ((unsigned long long)((s_min >> top) << top) << 32);
     __syncthreads();
     const unsigned iters = (free_n + B - 1) / B;
-    // ---- select: rank m of the free_n composites (key, index) ----
-    for (int d = 0; d < kPasses; ++d) {
+    // ---- select: rank m of the free_n composites (key, index); bits [hi, 64) are resolved ----
+    int hi = 32 + top;
+    for (int pass = 0; pass < 8; ++pass) {
         for (unsigned t = tid; t < (unsigned)kBins; t += B) hist[t] = 0;
         __syncthreads();
         if (s_done) break;
         const unsigned long long prefix = s_prefix;
-        const int dsh = dshift(d), psh = d ? dshift(d - 1) : 64;
-        const unsigned mask = (1u << dbits(d)) - 1u;
+        const int dsh = hi > 32 ? max(hi - DBITS, 32) : max(hi - DBITS, 0);  // digits never straddle key | index
+        const unsigned mask = (1u << (hi - dsh)) - 1u;
         for (unsigned it = 0; it < iters; ++it) {
             const unsigned i = it * B + tid;
             bool valid = i < free_n;
             const unsigned key = valid ? skey[i] : 0u;
             unsigned digit;
             if (dsh >= 32) {   // a digit of the key
-                if (d > 0) valid = valid && ((key >> (psh - 32)) == (unsigned)(prefix >> psh));
+                if (hi < 64) valid = valid && ((key >> (hi - 32)) == (unsigned)(prefix >> hi));
                 digit = (key >> (dsh - 32)) & mask;
             } else {           // a digit of the point index, among the elements whose key equals the node's
                 valid = valid && key == (unsigned)(prefix >> 32);
                 const unsigned id = valid ? (unsigned)src.idx[lo + i] : 0u;
-                if (psh < 32) valid = valid && ((id >> psh) == ((unsigned)(prefix & 0xffffffffull) >> psh));
+                if (hi < 32) valid = valid && ((id >> hi) == ((unsigned)(prefix & 0xffffffffull) >> hi));
                 digit = (id >> dsh) & mask;
             }
             warp_hist_add(hist, digit, valid);
@@ -634,50 +650,20 @@ __global__ void __launch_bounds__(512, (NCOL <= 4 ? 3 : 1)) k_medium(Cols src, C
             }
         __syncthreads();
         if (tid == 0) {
-            if (s_bin < 0) { atomicExch(err, 11 + d); s_done = 1; }
+            if (s_bin < 0) { atomicExch(err, 11 + pass); s_done = 1; }
             else {
                 s_prefix = prefix | ((unsigned long long)(unsigned)s_bin << dsh);
                 s_rank = r - s_cum;
                 s_shift = dsh;
-                if (s_cnt == 1u || d == kPasses - 1) s_done = 1;
+                if (s_cnt == 1u || dsh == 0) s_done = 1;
             }
         }
+        hi = dsh;
         __syncthreads();
     }
     __syncthreads();
     const int shift = s_shift;
     const unsigned long long want = s_prefix >> shift;
-    const unsigned nodekey = (unsigned)(s_prefix >> 32);  // complete only when shift < 32
-    // side of element i: -1 left, 0 node, 1 right.  The index is read only when the key alone cannot decide.
-    auto classify = [&](unsigned i, unsigned key, unsigned& id, bool& have_id) -> int {
-        have_id = false;
-        id = 0;
-        if (shift < 32 && key == nodekey) { id = (unsigned)src.idx[lo + i]; have_id = true; }
-        const unsigned long long c = composite(key, id) >> shift;
-        return c < want ? -1 : (c > want ? 1 : 0);
-    };
-    // ---- the left range's maximum (key first, index among equal keys) ----
-    unsigned kmax = 0;
-    bool any_left = false;
-    for (unsigned i = tid; i < free_n; i += B) {
-        unsigned id; bool have;
-        const unsigned key = skey[i];
-        if (classify(i, key, id, have) == -1) { kmax = any_left ? max(kmax, key) : key; any_left = true; }
-    }
-    for (int o = 16; o > 0; o >>= 1) kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
-    if (lane == 0 && kmax) atomicMax(&s_kmax, kmax);
-    __syncthreads();
-    kmax = s_kmax;
-    for (unsigned i = tid; i < free_n; i += B) {
-        const unsigned key = skey[i];
-        if (key != kmax) continue;
-        unsigned id; bool have;
-        if (classify(i, key, id, have) != -1) continue;
-        if (!have) id = (unsigned)src.idx[lo + i];
-        atomicMax(&s_best, ((unsigned long long)id << 32) | i);
-    }
-    __syncthreads();
-    const unsigned pmax = (unsigned)(s_best & 0xffffffffull);  // position (inside the range) of the left maximum
     // ---- move the points: loads of four elements per thread are issued before any of them is ranked ----
     if (tid == 0) {  // the pinned element keeps its slot: last of the right range
         const unsigned p = lo + n - 1;
@@ -685,6 +671,8 @@ __global__ void __launch_bounds__(512, (NCOL <= 4 ? 3 : 1)) k_medium(Cols src, C
         for (int c = 0; c < NCOL; ++c) dst.c[c][p] = src.c[c][p];
         dst.idx[p] = src.idx[p];
     }
+    unsigned long long best = 0ull;   // largest left-going composite seen by this thread, and where it went
+    unsigned bestpos = 0xffffffffu;
     constexpr int U = 4;
     for (unsigned it = 0; it < iters; it += U) {
         float val[U][NCOL > 0 ? NCOL : 1];
@@ -701,10 +689,11 @@ __global__ void __launch_bounds__(512, (NCOL <= 4 ? 3 : 1)) k_medium(Cols src, C
         for (int u = 0; u < U; ++u) {
             const unsigned i = (it + u) * B + tid;
             int side = 2;
+            unsigned long long comp = 0ull;
             if (i < free_n) {
-                const unsigned long long c = composite(skey[i], (unsigned)id[u]) >> shift;
+                comp = composite(skey[i], (unsigned)id[u]);
+                const unsigned long long c = comp >> shift;
                 side = c < want ? -1 : (c > want ? 1 : 0);
-                if (i == pmax) side = -2;  // the left maximum: goes to the left range's last slot
             }
             const unsigned bl = __ballot_sync(0xffffffffu, side == -1);
             const unsigned br = __ballot_sync(0xffffffffu, side == 1);
@@ -727,13 +716,38 @@ __global__ void __launch_bounds__(512, (NCOL <= 4 ? 3 : 1)) k_medium(Cols src, C
                 }
                 continue;
             }
-            unsigned p;
-            if (side == -2) p = lo + m - 1;
-            else if (side == -1) p = lo + wl + __popc(bl & lt);
-            else p = lo + m + 1 + wr + __popc(br & lt);
+            const unsigned p = side == -1 ? lo + wl + __popc(bl & lt) : lo + m + 1 + wr + __popc(br & lt);
 #pragma unroll
             for (int c = 0; c < NCOL; ++c) dst.c[c][p] = val[u][c];
             dst.idx[p] = id[u];
+            if (side == -1 && (bestpos == 0xffffffffu || comp > best)) { best = comp; bestpos = p; }
+        }
+    }
+    // ---- the left range's maximum goes to the left range's last slot (it is pinned one level down) ----
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long oc = __shfl_xor_sync(0xffffffffu, best, o);
+        const unsigned op = __shfl_xor_sync(0xffffffffu, bestpos, o);
+        if (op != 0xffffffffu && (bestpos == 0xffffffffu || oc > best)) { best = oc; bestpos = op; }
+    }
+    if (lane == 0) { s_bcomp[wid] = best; s_bpos[wid] = bestpos; }
+    __threadfence();
+    __syncthreads();   // every store of the sweep is visible to the thread that swaps
+    if (tid == 0) {
+        best = 0ull;
+        bestpos = 0xffffffffu;
+        for (unsigned w = 0; w < (B >> 5); ++w)
+            if (s_bpos[w] != 0xffffffffu && (bestpos == 0xffffffffu || s_bcomp[w] > best)) { best = s_bcomp[w]; bestpos = s_bpos[w]; }
+        const unsigned last = lo + m - 1;
+        if (bestpos != 0xffffffffu && bestpos != last) {
+#pragma unroll
+            for (int c = 0; c < NCOL; ++c) {
+                const float a = __ldcg(&dst.c[c][bestpos]), b2 = __ldcg(&dst.c[c][last]);
+                dst.c[c][bestpos] = b2;
+                dst.c[c][last] = a;
+            }
+            const int32_t a = __ldcg(&dst.idx[bestpos]), b2 = __ldcg(&dst.idx[last]);
+            dst.idx[bestpos] = b2;
+            dst.idx[last] = a;
         }
     }
 }
