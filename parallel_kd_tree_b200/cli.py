@@ -7,7 +7,7 @@ kdtree_mpi.cpp:170-291).
     torchrun --nproc-per-node W -m parallel_kd_tree_b200 mpi ...   # one rank per GPU, peer-memory min-reduce
 
 stdout carries READY / the result lines / DONE, stderr the prompts, exactly like the reference.
-Extra switches (ours): --device, --print-tree, --print-head.
+Extra switches (ours): --device, --print-tree, --print-head, --trace.
 """
 from __future__ import annotations
 
@@ -19,7 +19,7 @@ import torch
 
 from . import ops
 from .models import Forest, KDTree
-from .utils import protocol
+from .utils import protocol, trace
 from .utils.timing import PhaseTimer
 
 
@@ -38,7 +38,8 @@ def run_sequential(args, positional) -> int:
         seed, dim, n = protocol.specify_problem_stdin()
     dev = _device(args.device)
     nq = protocol.NUM_QUERIES
-    pts, qs = ops.generate_problem(seed, dim, n, nq)      # last rows are the queries (kdtree_sequential.cpp:156-157)
+    with trace.span("generate"):
+        pts, qs = ops.generate_problem(seed, dim, n, nq)  # last rows are the queries (kdtree_sequential.cpp:156-157)
     tree = KDTree(pts.to(dev))
     res = tree.nearest(qs.to(dev))
     dist = res.dist.cpu()
@@ -90,10 +91,18 @@ def main(argv=None) -> int:
     ap.add_argument("--world", type=int, default=16, help="ranks of the forest (reference: mpirun -np 16, Makefile:36)")
     ap.add_argument("--print-tree", action="store_true")
     ap.add_argument("--print-head", action="store_true")
+    ap.add_argument("--trace", action="store_true", help="per-phase timings on stderr (ours)")
     args, positional = ap.parse_known_args(argv)
-    if args.program == "sequential":
-        return run_sequential(args, positional)
-    return run_mpi(args, positional)
+    if args.trace:
+        trace.enable()
+        trace.reset()
+    try:
+        if args.program == "sequential":
+            return run_sequential(args, positional)
+        return run_mpi(args, positional)
+    finally:
+        if args.trace:
+            trace.report()
 
 
 if __name__ == "__main__":

@@ -7,6 +7,7 @@ from dataclasses import dataclass
 import torch
 
 from .. import ops
+from ..utils import trace
 from .._lib import check, lib, take_string
 
 
@@ -40,7 +41,8 @@ class KDTree:
         self.n, self.dim = self.points.shape
         self.id_offset = int(id_offset)
         if _prebuilt is None:
-            self.perm, self.tree_points = ops.build(self.points)
+            with trace.span(f"build n={self.n} dim={self.dim}", self.points.device):
+                self.perm, self.tree_points = ops.build(self.points)
         else:
             self.perm, self.tree_points = _prebuilt
 
@@ -66,7 +68,8 @@ class KDTree:
         queries = queries.to(self.device, torch.float32)
         if queries.dim() == 1:
             queries = queries[None]
-        idx, d2, d, vis = ops.nearest(self.tree_points, self.perm, queries)
+        with trace.span(f"nearest nq={queries.shape[0]}", self.device):
+            idx, d2, d, vis = ops.nearest(self.tree_points, self.perm, queries)
         return NNResult(index=idx, ids=idx + (1 + self.id_offset), dist2=d2, dist=d, visited=vis)
 
     def knn(self, queries: torch.Tensor, k: int):

@@ -102,3 +102,12 @@ def test_mpi_program_under_torchrun_gloo_two_ranks(oracle):
     out = [ln for ln in r.stdout.splitlines() if ln.startswith(("READY", "ID:", "DONE"))]
     assert out[0] == "READY" and out[-1] == "DONE"
     assert "\n".join(out[1:11]) + "\n" == oracle.forest_lines(3, 3, 4001, 10, 2)
+
+
+def test_trace_switch_reports_phases_on_stderr_only(oracle):
+    r = run_cli(["sequential", "--device", "cpu", "--trace", "7", "3", "5000"])
+    assert r.returncode == 0
+    assert "[kd trace] generate" in r.stderr and "[kd trace] build n=5000 dim=3" in r.stderr
+    assert "kd trace" not in r.stdout
+    from parallel_kd_tree_b200.utils import trace
+    trace.enable(False)
