@@ -49,6 +49,9 @@ int64_t kd_root_slot(int64_t n);
 /* checks shape-independent invariants of a perm built with the reference rule; returns #violations in *bad. */
 int kd_check_tree_cpu(const float* points, int64_t n, int dim, const int32_t* perm, int64_t* bad);
 
+/* the same check with ties allowed on either side: 0 violations = a possible output of the reference's unstable sort */
+int kd_check_tree_ties_cpu(const float* points, int64_t n, int dim, const int32_t* perm, int64_t* bad);
+
 /* ---- text protocol (Utility.cpp:21-63,122-124; Node.cpp:16-28) ---- */
 int kd_format_float(float v, char* buf, int cap);
 int kd_format_result_line(int id, float distance, char* buf, int cap);

@@ -40,6 +40,7 @@ def _declare(lib):
         "kd_materialize_nodes_cpu": (i32, [i64, vp, vp, vp, vp]),
         "kd_root_slot": (i64, [i64]),
         "kd_check_tree_cpu": (i32, [vp, i64, i32, vp, vp]),
+        "kd_check_tree_ties_cpu": (i32, [vp, i64, i32, vp, vp]),
         "kd_format_float": (i32, [f32, C.c_char_p, i32]),
         "kd_format_result_line": (i32, [i32, f32, C.c_char_p, i32]),
         "kd_format_point": (i32, [vp, i32, i32, C.POINTER(vp), C.POINTER(C.c_size_t)]),

@@ -375,6 +375,41 @@ int kd_check_tree_cpu(const float* points, int64_t n, int dim, const int32_t* pe
     return 0;
 }
 
+int kd_check_tree_ties_cpu(const float* points, int64_t n, int dim, const int32_t* perm, int64_t* bad) {
+    // Tie-tolerant form of kd_check_tree_cpu: equal coordinates may fall on either side (what an unstable
+    // std::sort is free to do).  A permutation with 0 violations is a possible output of
+    // the reference's build_tree on this input.
+    if (!points || !perm || !bad || n <= 0 || dim <= 0) return kd::fail("kd_check_tree_ties_cpu: bad arguments");
+    int64_t v = 0;
+    std::vector<uint8_t> seen((size_t)n, 0);
+    for (int64_t i = 0; i < n; ++i) {
+        if (perm[i] < 0 || perm[i] >= n || seen[perm[i]]) ++v; else seen[perm[i]] = 1;
+    }
+    if (v) { *bad = v; return 0; }
+    struct R { int64_t lo, n; int depth; };
+    std::vector<R> st{{0, n, 0}};
+    while (!st.empty()) {
+        R r = st.back();
+        st.pop_back();
+        if (r.n < 3) continue;
+        const int axis = r.depth % dim;
+        auto key = [&](int64_t slot) { return points[(size_t)perm[slot] * dim + axis]; };
+        int64_t m = r.n / 2;
+        float node = key(r.lo + m);
+        for (int64_t i = r.lo; i < r.lo + m; ++i)
+            if (key(i) > node) ++v;
+        for (int64_t i = r.lo + m + 1; i < r.lo + r.n - 1; ++i)
+            if (key(i) < node) ++v;
+        float lmax = key(r.lo + m - 1);
+        for (int64_t i = r.lo; i + 1 < r.lo + m; ++i)
+            if (key(i) > lmax) ++v;
+        st.push_back({r.lo, m, r.depth + 1});
+        st.push_back({r.lo + m + 1, r.n - m - 1, r.depth + 1});
+    }
+    *bad = v;
+    return 0;
+}
+
 int kd_format_float(float v, char* buf, int cap) {
     std::string s = fmt_float(v);
     if ((int)s.size() + 1 > cap) return kd::fail("kd_format_float: buffer too small");

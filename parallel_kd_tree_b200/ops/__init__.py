@@ -1,8 +1,8 @@
 """Torch-level operators of the B200 kd-tree library.
 
 Every operator is registered as a ``torch.library`` custom op in the ``kd``
-namespace (``torch.ops.kd.build`` ...) and dispatches on the device of its
-inputs: CUDA tensors run the hand-written sm_100a kernels of
+namespace (``torch.ops.kd.build`` ...; the Python functions of this module call the
+same implementations directly) and dispatches on the device of its inputs: CUDA tensors run the hand-written sm_100a kernels of
 ``libkdtree_b200.so``, CPU tensors run the native C++ host core of the same
 library (a few trivial CPU helpers — bbox, row gather — use plain torch).  CUDA
 inputs never fall back to PyTorch eager code: if the library is missing the op raises.

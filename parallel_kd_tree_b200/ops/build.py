@@ -41,14 +41,18 @@ def build_into(points: torch.Tensor, perm: torch.Tensor, tree_points: torch.Tens
             torch.index_select(points, 0, perm.long(), out=tree_points)
 
 
-@torch.library.custom_op("kd::build", mutates_args=())
-def _build_op(points: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
+def _build_impl(points: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
     points = as_points(points)
     n, dim = points.shape
     perm = torch.empty(n, dtype=torch.int32, device=points.device)
     tree_points = torch.empty((n, dim), dtype=torch.float32, device=points.device)
     build_into(points, perm, tree_points, verify=True)
     return perm, tree_points
+
+
+# registered as torch.ops.kd.build; the Python entry point below calls the implementation directly (the first
+# trip through the dispatcher of a custom op costs seconds of lazy imports, which a CLI run would pay every time)
+_build_op = torch.library.custom_op("kd::build", mutates_args=())(_build_impl)
 
 
 @_build_op.register_fake
@@ -64,7 +68,7 @@ def build(points: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
     ``perm[lo + n//2]``, its sub-trees are ``[lo, lo+n//2)`` and ``[lo+n//2+1, lo+n)``
     (kdtree_sequential.cpp:51-56).  ``tree_points[s] = points[perm[s]]``.
     """
-    return torch.ops.kd.build(points)
+    return _build_impl(points)
 
 
 def build_cpu_sortref(points: torch.Tensor) -> torch.Tensor:
@@ -76,11 +80,15 @@ def build_cpu_sortref(points: torch.Tensor) -> torch.Tensor:
     return perm
 
 
-def check_tree(points: torch.Tensor, perm: torch.Tensor) -> int:
-    """Number of violations of the reference's construction rule in ``perm`` (0 = the unique correct tree)."""
+def check_tree(points: torch.Tensor, perm: torch.Tensor, allow_ties: bool = False) -> int:
+    """Number of violations of the reference's construction rule in ``perm``.
+
+    Strict (default): 0 = the unique tree under the canonical tie-break (coordinate, index).
+    ``allow_ties``: equal coordinates may fall on either side; 0 = a possible output of the reference's
+    unstable ``std::sort`` (used to validate the unmodified reference's trees at scale)."""
     points = as_points(points).cpu()
     perm = perm.to("cpu", torch.int32).contiguous()
     bad = C.c_int64(0)
-    check(lib().kd_check_tree_cpu(points.data_ptr(), points.shape[0], points.shape[1], perm.data_ptr(),
-                                  C.addressof(bad)), "check_tree")
+    fn = lib().kd_check_tree_ties_cpu if allow_ties else lib().kd_check_tree_cpu
+    check(fn(points.data_ptr(), points.shape[0], points.shape[1], perm.data_ptr(), C.addressof(bad)), "check_tree")
     return int(bad.value)

@@ -7,8 +7,7 @@ from .._lib import check, lib
 from ._util import as_points, stream_ptr
 
 
-@torch.library.custom_op("kd::nearest", mutates_args=())
-def _nearest_op(tree_points: torch.Tensor, perm: torch.Tensor,
+def _nearest_op_impl(tree_points: torch.Tensor, perm: torch.Tensor,
                 queries: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
     tree_points = as_points(tree_points, "tree_points")
     queries = as_points(queries, "queries")
@@ -40,6 +39,9 @@ def _nearest_op(tree_points: torch.Tensor, perm: torch.Tensor,
     return idx, d2, d, vis
 
 
+_nearest_op = torch.library.custom_op("kd::nearest", mutates_args=())(_nearest_op_impl)
+
+
 @_nearest_op.register_fake
 def _(tree_points, perm, queries):
     nq = queries.shape[0]
@@ -49,7 +51,7 @@ def _(tree_points, perm, queries):
 
 def nearest(tree_points: torch.Tensor, perm: torch.Tensor, queries: torch.Tensor):
     """1-NN of every query with the reference's traversal; returns (point index, dist², dist, nodes visited)."""
-    return torch.ops.kd.nearest(tree_points, perm, queries)
+    return _nearest_op_impl(tree_points, perm, queries)
 
 
 def gather_rows(points: torch.Tensor, perm: torch.Tensor) -> torch.Tensor:
@@ -63,8 +65,7 @@ def gather_rows(points: torch.Tensor, perm: torch.Tensor) -> torch.Tensor:
     return out
 
 
-@torch.library.custom_op("kd::materialize_nodes", mutates_args=())
-def _materialize_op(perm: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+def _materialize_op_impl(perm: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
     perm = perm.to(torch.int32).contiguous()
     n = perm.numel()
     node_point, left, right = (torch.empty_like(perm) for _ in range(3))
@@ -78,6 +79,9 @@ def _materialize_op(perm: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor, tor
     return node_point, left, right
 
 
+_materialize_op = torch.library.custom_op("kd::materialize_nodes", mutates_args=())(_materialize_op_impl)
+
+
 @_materialize_op.register_fake
 def _(perm):
     return torch.empty_like(perm), torch.empty_like(perm), torch.empty_like(perm)
@@ -85,11 +89,10 @@ def _(perm):
 
 def materialize_nodes(perm: torch.Tensor):
     """``Node{point,left,right}`` (Node.hpp:35-45) as int32 arrays indexed by slot; -1 = nullptr; root = n//2."""
-    return torch.ops.kd.materialize_nodes(perm)
+    return _materialize_op_impl(perm)
 
 
-@torch.library.custom_op("kd::bbox", mutates_args=())
-def _bbox_op(points: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
+def _bbox_op_impl(points: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
     points = as_points(points)
     if not points.is_cuda:
         return points.min(0).values, points.max(0).values
@@ -102,6 +105,9 @@ def _bbox_op(points: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
     return mn, mx
 
 
+_bbox_op = torch.library.custom_op("kd::bbox", mutates_args=())(_bbox_op_impl)
+
+
 @_bbox_op.register_fake
 def _(points):
     return points.new_empty(points.shape[1]), points.new_empty(points.shape[1])
@@ -109,7 +115,7 @@ def _(points):
 
 def bbox(points: torch.Tensor):
     """Per-axis (min, max) of a point set."""
-    return torch.ops.kd.bbox(points)
+    return _bbox_op_impl(points)
 
 
 def knn(tree_points: torch.Tensor, perm: torch.Tensor, queries: torch.Tensor, k: int):
