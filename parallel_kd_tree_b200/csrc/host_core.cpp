@@ -220,9 +220,12 @@ int kd_nearest_cpu(const float* points, int64_t n, int dim, const int32_t* perm,
         }
         return dist;
     };
+    // queries are independent: one contiguous block of them per hardware thread
+    const int workers = (int)std::max<int64_t>(1, std::min<int64_t>(std::thread::hardware_concurrency(), nq / 4));
+    auto run = [&](int64_t q0, int64_t q1) {
     std::vector<Far> st;
     st.reserve(64);
-    for (int64_t q = 0; q < nq; ++q) {
+    for (int64_t q = q0; q < q1; ++q) {
         const float* qp = queries + (size_t)q * dim;
         int64_t root = n / 2;
         int32_t best = perm[root];
@@ -269,6 +272,11 @@ int kd_nearest_cpu(const float* points, int64_t n, int dim, const int32_t* perm,
         if (out_dist) out_dist[q] = std::sqrt(best_d);
         if (out_visited) out_visited[q] = visited;
     }
+    };
+    std::vector<std::thread> pool;
+    for (int w = 1; w < workers; ++w) pool.emplace_back(run, nq * w / workers, nq * (w + 1) / workers);
+    run(0, nq / workers);
+    for (auto& t : pool) t.join();
     return 0;
 }
 
