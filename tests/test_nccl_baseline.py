@@ -28,6 +28,11 @@ for n, dim, seed in [(5003, 3, 1), (20000, 2, 2), (4099, 1, 3)]:
     same = torch.equal(perm, ref)
     ok &= same
     print(f"rank {rank} n={n} dim={dim}: {'OK' if same else 'MISMATCH'}", flush=True)
+from parallel_kd_tree_b200.parallel.bbox import distributed_bbox
+allp = kd.ops.generate_uniform(9, 5, 4001)
+first, local = kd.models.slice_bounds(4001, world, rank)
+mn, mx = distributed_bbox(allp[first:first + local])
+ok &= torch.equal(mn, allp.min(0).values) and torch.equal(mx, allp.max(0).values)
 g = torch.Generator().manual_seed(7)
 pts = torch.randint(-3, 4, (9001, 3), generator=g).float()
 first, local = kd.models.slice_bounds(9001, world, rank)
