@@ -120,6 +120,14 @@ class KDTree:
         """Serialisable form (the reference never serialises its tree; SURVEY.md §5 checkpoint row)."""
         return {"points": self.points.cpu(), "perm": self.perm.cpu(), "id_offset": self.id_offset}
 
+    def save(self, path) -> None:
+        """Writes ``state_dict()`` with ``torch.save`` (checkpoint; the reference keeps its tree in memory only)."""
+        torch.save(self.state_dict(), path)
+
+    @classmethod
+    def load(cls, path, device: str | torch.device = "cpu") -> "KDTree":
+        return cls.from_state_dict(torch.load(path, map_location="cpu"), device)
+
     @classmethod
     def from_state_dict(cls, state: dict, device: str | torch.device = "cpu") -> "KDTree":
         pts = state["points"].to(device)

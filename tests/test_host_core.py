@@ -118,6 +118,11 @@ def test_state_dict_roundtrip(kd):
     tree = kd.KDTree(pts)
     again = kd.KDTree.from_state_dict(tree.state_dict())
     assert torch.equal(again.perm, tree.perm)
+    import os, tempfile
+    with tempfile.TemporaryDirectory() as tmp:
+        tree.save(os.path.join(tmp, "tree.pt"))
+        loaded = kd.KDTree.load(os.path.join(tmp, "tree.pt"))
+    assert torch.equal(loaded.perm, tree.perm) and torch.equal(loaded.tree_points, tree.tree_points)
     assert torch.equal(again.nearest(qs).dist, tree.nearest(qs).dist)
 
 
