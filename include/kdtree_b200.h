@@ -64,7 +64,8 @@ int kd_format_head_and_leaves(const float* points, int64_t n, int dim, const int
 /* ---- single-GPU build (new; semantics of kdtree_sequential.cpp:30-66) ---- */
 size_t kd_build_workspace_bytes(int64_t n, int dim);
 /* points: device float32 [n][dim]; perm: device int32[n]; tree_points (optional, may be NULL): device
- * float32 [n][dim] receiving the coordinates in in-order slot order. */
+ * float32 [n][dim] receiving the coordinates in in-order slot order; workspace: 256-byte aligned device memory
+ * of kd_build_workspace_bytes(n, dim) bytes (the TMA bulk copies of the finisher need aligned columns). */
 int kd_build_gpu(const float* points, int64_t n, int dim, int32_t* perm, float* tree_points, void* workspace,
                  size_t workspace_bytes, void* stream);
 /* The same build for callers that cannot allocate device memory (code running inside someone else's fixed
