@@ -32,6 +32,8 @@ void kd_free(void* p); /* releases buffers returned by the kd_format_* functions
 int kd_generate_uniform(int seed, int dim, int64_t n_rows, float* out);
 /* rows [first_row, first_row + n_rows) of the same stream (O(first_row) skip-ahead). */
 int kd_generate_uniform_rows(int seed, int dim, int64_t first_row, int64_t n_rows, float* out);
+/* number of mismatches between the library's per-draw arithmetic and libstdc++'s distribution object (0 expected) */
+int64_t kd_generator_selftest(int seed, int64_t count);
 /* seeded Gaussian blobs (not in the reference; BASELINE.json config 4). */
 int kd_generate_clustered(int seed, int dim, int64_t n_rows, int n_clusters, float sigma, float* out);
 

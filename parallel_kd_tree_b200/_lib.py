@@ -33,6 +33,7 @@ def _declare(lib):
         "kd_free": (None, [vp]),
         "kd_generate_uniform": (i32, [i32, i32, i64, vp]),
         "kd_generate_uniform_rows": (i32, [i32, i32, i64, i64, vp]),
+        "kd_generator_selftest": (i64, [i32, i64]),
         "kd_generate_clustered": (i32, [i32, i32, i64, i32, f32, vp]),
         "kd_build_cpu": (i32, [vp, i64, i32, vp, i32]),
         "kd_build_cpu_sortref": (i32, [vp, i64, i32, vp]),

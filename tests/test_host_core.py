@@ -143,3 +143,8 @@ def test_knn_extension_cpu(kd):
     assert torch.equal(ids.long() - 1, brute.indices)
     ids, d = kd.KDTree(pts[:3]).knn(qs, 5)
     assert (ids[:, 3:] == -1).all() and torch.isinf(d[:, 3:]).all()
+
+
+def test_generator_arithmetic_matches_libstdcxx_objects(kd):
+    for seed in (1, 7, 12345):
+        assert kd.lib().kd_generator_selftest(seed, 3_000_000) == 0
