@@ -14,8 +14,8 @@
 //       k_hist + k_scan                 ~10 % candidates, MSB radix select on the composite (key, index) over them
 //   K3  k_partition + k_fixup           large ranges: unstable three-way partition, node emission, left-max -> last slot
 //   K2+K3  k_medium                     ranges of 513..16384 points: one CTA selects and partitions in one kernel
-//   K4  k_finish                        windows of <= kFinishT slots: whole sub-trees inside shared memory
-//                                       (TMA-staged, register/shuffle bitonic networks)
+//   K4  k_subtree                       windows of <= kFinishT slots: whole sub-trees inside shared memory
+//                                       (TMA-staged, per-level radix select + partition in registers / shuffles)
 //
 // Ranges are never stored: range s of level l is found by walking the shape
 // rule (left n/2, right n-n/2-1) along the bits of s.
@@ -24,6 +24,8 @@
 #include <algorithm>
 #include <cstdint>
 #include <cstdio>
+#include <mutex>
+#include <string>
 
 #include "../../include/kdtree_b200.h"
 #include "build_plan.h"
@@ -541,7 +543,7 @@ __global__ void __launch_bounds__(256) k_fixup(Cols dst, int ncol, const MaxRec*
 }
 
 // ------------------------------------------------------------------------------------------
-// K2+K3 for medium ranges (kFinishEff < n <= kMediumMax): ONE CTA owns the range for the whole
+// K2+K3 for medium ranges (kFinishT < n <= kMediumMax): ONE CTA owns the range for the whole
 // level.  The split-axis keys are staged in shared memory once, every digit pass of the select
 // runs on them (shared-memory histogram, no global atomics, no global histogram), then a single
 // sweep moves the points: the node to its final slot, the left range's maximum straight to the left
@@ -752,16 +754,6 @@ __global__ void __launch_bounds__(512, (NCOL <= 4 ? 3 : 1)) k_medium(Cols src, C
     }
 }
 
-// ------------------------------------------------------------------------------------------
-// K4: finisher.  One CTA owns a range of n <= kFinishT points and builds its whole sub-tree
-// in shared memory.  Per sub-level every sub-range's first n-1 positions are sorted on the
-// sub-level's axis (the reference's own formulation, kdtree_sequential.cpp:46-56) by ONE
-// bitonic network over 4096 virtual positions (sub-range s owns the P-aligned block s, padded
-// with +inf): each thread keeps 8 consecutive virtual positions in registers, partners at
-// distance < 8 are exchanged in registers, < 256 with warp shuffles, the few larger ones through
-// shared memory.  Points never move, a (key, slot) pair does; all slots are final at the end and
-// are written out once, coalesced.
-// ------------------------------------------------------------------------------------------
 // TMA (bulk async copy engine) helpers: 1-D global -> shared copies completing on an mbarrier.
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
@@ -798,62 +790,356 @@ __device__ __forceinline__ bool mbar_wait(unsigned long long* bar, unsigned pari
     return false;
 }
 
-constexpr int kFinishBlock = 512;
-constexpr int kFinishEpt = kFinishT / kFinishBlock;
-constexpr unsigned kInfKey = 0xffffffffu, kInfSlot = 0xffffu;
-static_assert(kFinishEpt == 8, "the finisher network is written for 8 elements per thread");
+// ------------------------------------------------------------------------------------------
+// K4: shared-memory sub-tree builder.  One CTA owns a window of n <= kFinishT points and builds
+// its whole sub-tree (up to 12 levels) with ONE trip through HBM: the window is staged with the TMA
+// engine, every level is a select + partition on (key, index) composites that never leaves the SM,
+// and the finished window is written out once, coalesced, to every replica of the tree arrays.
+//
+// What a level has to produce (kdtree_sequential.cpp:46-56, restated without the sort): the element
+// of rank n/2 among the sub-range's first n-1 positions (the node), the smaller ones on its left with
+// their maximum in the left part's last position (it is pinned one level down), the larger ones on its
+// right, the old pinned element untouched.  Points never move: `sord` maps position -> staged slot and
+// is permuted in place (every team reads its positions into registers before it writes them).
+//
+// Virtual layout: sub-range q of sub-level j owns the P-aligned block q of P0 = pow2 >= n virtual
+// positions (P = P0 >> j >= its size), 8 consecutive virtual positions per thread, so the threads of
+// sub-range q are an aligned group of P/8 threads, a "team":
+//   P >= 512       team = 2..16 warps  -> counts meet in shared memory, __syncthreads between phases
+//   16 <= P <= 256 team = 2..32 lanes  -> every warp runs on its own (no CTA barrier until the write-out);
+//                                         counts are warp reductions over the team's lanes (REDUX)
+//   P <= 8         a thread owns whole sub-ranges -> all-pairs ranks in registers (that IS the sort)
+// Select of a team: MSB radix select with 4-bit digits aligned to the range of the keys that are still
+// alive (key - min, so the first digit already splits >= 8 ways; index digits only among equal keys).
+// No shared-memory atomics per element: each thread counts its 8 elements into sixteen 4-bit fields of
+// a 64-bit register, the fields are widened to 16 bits and summed with 8 warp reductions.  As soon as
+// at most `cap` elements are alive they are compacted into a team list (ballot ranks) and resolved by
+// all-pairs counting, which yields the node's composite X and, if the node is not the smallest
+// candidate, the left maximum M; otherwise M is a max-reduction over the elements below X.
+// ------------------------------------------------------------------------------------------
+constexpr int kSubBlock = 512;
+constexpr int kSubWarps = kSubBlock / 32;
+static_assert(kSubBlock * 8 == kFinishT, "8 virtual positions per thread");
+constexpr unsigned kSubListPerWarp = 128;                 // candidate slots (u64) per warp
+constexpr unsigned kSubWarpScratch = kSubListPerWarp + 32; // + (X, M) for up to 16 teams of the warp
+constexpr unsigned kSubCap = 64;                           // candidates resolved by all-pairs counting
+constexpr int kSubTS = kFinishT + 8;                       // column stride (the staged window starts 16-byte aligned)
 
-// Compare-exchange on (key, point index, slot) triples.  (key, index) is a strict total order, so no tie
-// path exists: two 32-bit compares, one predicate op, three selects.  Padding is (kInfKey, 0xffffffff, kInfSlot);
-// two paddings compare equal and may be "swapped", which changes nothing.
-__device__ __forceinline__ bool fin_before(unsigned ak, unsigned ai, unsigned bk, unsigned bi) {
-    return (((unsigned long long)ak << 32) | ai) < (((unsigned long long)bk << 32) | bi);
-}
+struct SubTeam { unsigned kmin, kmax, lcnt, pad; };       // shared state of a multi-warp team
 
-// keep the smaller (keep_min) or the larger of (mine, partner's)
-__device__ __forceinline__ void fin_ce_partner(unsigned& key, unsigned& idx, unsigned& slot, unsigned ok, unsigned oi,
-                                               unsigned os, bool keep_min) {
-    const bool take = fin_before(ok, oi, key, idx) == keep_min;
-    key = take ? ok : key;
-    idx = take ? oi : idx;
-    slot = take ? os : slot;
-}
+struct SubCtx {
+    float* scol;                 // [ncol][kSubTS] coordinates by slot
+    int32_t* sidx;               // [kSubTS]       point index by slot
+    unsigned long long* slist;   // [kSubWarps][kSubWarpScratch]
+    SubTeam* steam;              // [8]
+    unsigned* sbins;             // [3][8 teams][8 words]
+    unsigned* swtot;             // [kSubWarps]
+    unsigned* stab;              // [2][kFinishT / 2]  sub-range table (lo << 16 | n), by level parity
+    unsigned short* sord;        // [kFinishT]     slot by position
+    const float* pts;            // gather mode (ncol == 0): keys come from the point array
+    int ncol, dim;
+    int* err;
+};
 
-template <int S>
-__device__ __forceinline__ void fin_reg_step(unsigned (&key)[8], unsigned (&idx)[8], unsigned (&slot)[8], unsigned vbase,
-                                             unsigned k, bool last) {
-    const bool asc_hi = last || ((vbase & k) == 0u);  // k >= 8: the direction bit lives in the thread index
+__device__ __forceinline__ void sub_load(const SubCtx& C, int axis, unsigned slo, unsigned sn, unsigned i0,
+                                         unsigned long long (&comp)[8], unsigned (&slot)[8], unsigned& valid) {
+    const float* __restrict__ kcol = C.ncol ? C.scol + (size_t)axis * kSubTS : nullptr;
+    valid = 0u;
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-        if (e & S) continue;
-        const int f = e | S;
-        const bool asc = k >= 8u ? asc_hi : (last || ((e & k) == 0u));
-        const unsigned ke = key[e], kf = key[f], ie = idx[e], jf = idx[f], se = slot[e], sf = slot[f];
-        const bool sw = fin_before(kf, jf, ke, ie) == asc;  // out of order for this direction
-        key[e] = sw ? kf : ke;
-        key[f] = sw ? ke : kf;
-        idx[e] = sw ? jf : ie;
-        idx[f] = sw ? ie : jf;
-        slot[e] = sw ? sf : se;
-        slot[f] = sw ? se : sf;
+        const unsigned i = i0 + (unsigned)e;
+        comp[e] = ~0ull;
+        slot[e] = 0u;
+        if (sn >= 3u && i + 1u < sn) {   // position i of the sub-range's first n-1 (the last one is pinned)
+            const unsigned s = C.sord[slo + i];
+            const unsigned id = (unsigned)C.sidx[s];
+            const float f = kcol ? kcol[s] : C.pts[(size_t)id * C.dim + axis];
+            comp[e] = composite(ordered_key(f), id);
+            slot[e] = s;
+            valid |= 1u << e;
+        }
     }
 }
 
-__global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, const float* __restrict__ pts,
-                                                            int dim, unsigned N, int level, int depth0,
-                                                            OutPtrs out, unsigned out_lo, int skip) {
+// Team levels.  kCta: the team spans whole warps (P >= 512); otherwise it is an aligned group of lanes.
+template <bool kCta>
+__device__ __forceinline__ void sub_team_level(const SubCtx& C, int j, int logP, int axis) {
+    constexpr unsigned FULL = 0xffffffffu;
+    const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const int logT = logP - 3;                                     // log2(threads per team)
+    const unsigned tpt = 1u << logT, q = tid >> logT, tl = tid & (tpt - 1u);
+    const unsigned* tab = C.stab + (j & 1) * (kFinishT / 2);
+    unsigned* tabn = C.stab + ((j + 1) & 1) * (kFinishT / 2);
+    const bool in_range = q < (1u << j);
+    const unsigned ent = in_range ? tab[q] : 0u;
+    const unsigned slo = ent >> 16, sn = ent & 0xffffu, m = sn >> 1;
+    bool active = sn >= 3u;
+    const unsigned tmask = (kCta || tpt == 32u) ? FULL : (((1u << tpt) - 1u) << (lane & ~(tpt - 1u)));
+    const unsigned team_w0 = kCta ? ((q << logT) >> 5) : warp;
+    const unsigned tiw = kCta ? 0u : (lane >> logT);               // team index inside the warp
+    const unsigned tpw = kCta ? 1u : (32u >> logT);                // teams per warp
+    const unsigned lcap = kCta ? kSubCap : min(kSubCap, 4u * tpt);
+    unsigned long long* L = C.slist + (size_t)team_w0 * kSubWarpScratch + tiw * (kSubListPerWarp / tpw);
+    unsigned long long* XM = C.slist + (size_t)team_w0 * kSubWarpScratch + kSubListPerWarp + 2u * tiw;
+    auto tsync = [] { if (kCta) __syncthreads(); else __syncwarp(); };
+
+    unsigned long long comp[8];
+    unsigned slot[8], valid;
+    sub_load(C, axis, slo, sn, tl * 8u, comp, slot, valid);
+
+    // ---- range of the keys: the digits are aligned to it ----
+    unsigned kmn = 0xffffffffu, kmx = 0u;
+#pragma unroll
+    for (int e = 0; e < 8; ++e)
+        if ((valid >> e) & 1u) { const unsigned k = (unsigned)(comp[e] >> 32); kmn = min(kmn, k); kmx = max(kmx, k); }
+    kmn = __reduce_min_sync(tmask, kmn);
+    kmx = __reduce_max_sync(tmask, kmx);
+    if (kCta) {
+        SubTeam& T = C.steam[q];
+        if (lane == 0 && kmn <= kmx) { atomicMin(&T.kmin, kmn); atomicMax(&T.kmax, kmx); }
+        __syncthreads();
+        kmn = T.kmin;
+        kmx = T.kmax;
+    }
+    int mode = 0, sh = 0;      // mode 0: digits of (key - base); mode 1: digits of the point index (equal keys)
+    unsigned base = kmn, r = m, acnt = active ? sn - 1u : 0u, alive = valid;
+    if (active) {
+        if (kmn == kmx) { mode = 1; sh = 28; }
+        else { const int t = 31 - __clz(kmx - kmn); sh = t > 3 ? t - 3 : 0; }
+    }
+    // ---- radix select until at most lcap elements are alive ----
+    for (unsigned it = 0;; ++it) {
+        if (it >= 20u && active && acnt > lcap) {   // 16 digits always suffice: never spin on a logic error
+            if (tl == 0) atomicExch(C.err, 60 + j);
+            active = false; alive = 0u; valid = 0u; acnt = 0u;
+        }
+        const bool need = active && acnt > lcap;
+        if (kCta) { if (!__syncthreads_or(need ? 1 : 0)) break; }
+        else if (!__any_sync(FULL, need)) break;
+        unsigned long long acc = 0ull;
+        unsigned dig = 0u;
+        if (need) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const unsigned u = mode ? (unsigned)comp[e] : (unsigned)(comp[e] >> 32) - base;
+                const unsigned d = (u >> sh) & 15u;
+                if ((alive >> e) & 1u) { acc += 1ull << (4u * d); dig |= d << (4 * e); }
+            }
+        }
+        unsigned w[8];   // word k: bins 2k (low half) and 2k+1 (high half)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const unsigned byte = (unsigned)(acc >> (8 * k)) & 0xffu;
+            w[k] = __reduce_add_sync(tmask, (byte & 15u) | ((byte >> 4) << 16));
+        }
+        if (kCta) {
+            unsigned* B = C.sbins + (it % 3u) * 64u;
+            if (need && lane < 8u) {
+                unsigned v = w[0];
+#pragma unroll
+                for (int k = 1; k < 8; ++k) v = lane == (unsigned)k ? w[k] : v;
+                if (v) atomicAdd(&B[q * 8u + lane], v);
+            }
+            if (tid < 64u) C.sbins[((it + 2u) % 3u) * 64u + tid] = 0u;   // read two barriers ago, used two from now
+            __syncthreads();
+            if (need) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) w[k] = B[q * 8u + k];
+            }
+        }
+        if (need) {
+            unsigned cum = 0u, tb = 16u, cbase = 0u, ccnt = 0u;
+#pragma unroll
+            for (int b = 0; b < 16; ++b) {
+                const unsigned c = (w[b >> 1] >> (16 * (b & 1))) & 0xffffu;
+                if (tb == 16u && r < cum + c) { tb = (unsigned)b; cbase = cum; ccnt = c; }
+                cum += c;
+            }
+            if (tb == 16u) {   // the counts lost the wanted rank: internal error, leave the sub-range as it is
+                if (tl == 0) atomicExch(C.err, 40 + j);
+                active = false; alive = 0u; valid = 0u; acnt = 0u;
+            } else {
+                r -= cbase;
+                acnt = ccnt;
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                    if (((dig >> (4 * e)) & 15u) != tb) alive &= ~(1u << e);
+                if (mode == 0) {
+                    base += tb << sh;
+                    if (sh == 0) { mode = 1; sh = 28; } else sh = sh > 4 ? sh - 4 : 0;
+                } else {
+                    sh = sh >= 4 ? sh - 4 : 0;   // after the last index digit a single element is alive
+                }
+            }
+        }
+    }
+    // ---- the alive elements -> the team's list (ballot ranks; one atomic per warp for multi-warp teams) ----
+    {
+        const unsigned total = __reduce_add_sync(tmask, (unsigned)__popc(alive));
+        unsigned run = 0u;
+        if (kCta) {
+            if (lane == 0 && total) run = atomicAdd(&C.steam[q].lcnt, total);
+            run = __shfl_sync(FULL, run, 0);
+        }
+        const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const bool a = (alive >> e) & 1u;
+            const unsigned b = __ballot_sync(FULL, a) & tmask;
+            if (a) L[run + __popc(b & lt)] = comp[e];
+            run += __popc(b);
+        }
+        if (active && tl == 0 && r == 0u) XM[1] = 0ull;
+    }
+    tsync();
+    // ---- all-pairs ranks among the candidates: rank r is the node, rank r-1 the left maximum ----
+    for (unsigned ci = tl; ci < acnt; ci += tpt) {
+        const unsigned long long x = L[ci];
+        unsigned rk = 0u;
+        for (unsigned k = 0; k < acnt; ++k) rk += L[k] < x ? 1u : 0u;
+        if (rk == r) XM[0] = x;
+        if (rk + 1u == r) XM[1] = x;
+    }
+    tsync();
+    const unsigned long long X = active ? XM[0] : 0ull;
+    unsigned long long M = (active && r > 0u) ? XM[1] : 0ull;
+    {   // the node was the smallest candidate: the left maximum is the largest element below it
+        const bool needM = active && r == 0u;
+        const bool anyM = kCta ? (__syncthreads_or(needM ? 1 : 0) != 0) : (__any_sync(FULL, needM) != 0);
+        if (anyM) {
+            unsigned long long best = 0ull;
+            if (needM) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                    if (comp[e] < X && comp[e] > best) best = comp[e];
+            }
+            const unsigned hk = __reduce_max_sync(tmask, (unsigned)(best >> 32));
+            unsigned li = (best != 0ull && (unsigned)(best >> 32) == hk) ? (unsigned)best + 1u : 0u;
+            li = __reduce_max_sync(tmask, li);
+            if (kCta) {
+                if (needM && lane == 0 && li) atomicMax(&XM[1], ((unsigned long long)hk << 32) | (li - 1u));
+                __syncthreads();
+                if (needM) M = XM[1];
+            } else if (needM) {
+                M = ((unsigned long long)hk << 32) | (li - 1u);
+            }
+        }
+    }
+    // ---- new positions: left part (its maximum last), node, right part; the pinned element stays ----
+    unsigned cl = 0u, cr = 0u;
+#pragma unroll
+    for (int e = 0; e < 8; ++e)
+        if ((valid >> e) & 1u) {
+            if (comp[e] < X) cl += comp[e] != M ? 1u : 0u;
+            else if (comp[e] > X) ++cr;
+        }
+    const unsigned v = cl | (cr << 16);
+    unsigned incl = v;
+    const unsigned sw = kCta ? 32u : tpt;
+    for (unsigned o = 1; o < sw; o <<= 1) {
+        const unsigned t = __shfl_up_sync(FULL, incl, o, sw);
+        if ((lane & (sw - 1u)) >= o) incl += t;
+    }
+    unsigned ex = incl - v;
+    if (kCta) {
+        if (lane == 31) C.swtot[warp] = incl;
+        __syncthreads();
+        for (unsigned w2 = team_w0; w2 < warp; ++w2) ex += C.swtot[w2];
+    }
+    unsigned exL = ex & 0xffffu, exR = ex >> 16;
+#pragma unroll
+    for (int e = 0; e < 8; ++e)
+        if ((valid >> e) & 1u) {
+            unsigned pos;
+            if (comp[e] < X) pos = comp[e] == M ? m - 1u : exL++;
+            else pos = comp[e] == X ? m : m + 1u + exR++;
+            C.sord[slo + pos] = (unsigned short)slot[e];
+        }
+    if (in_range && tl == 0) {
+        tabn[2u * q] = (slo << 16) | m;
+        tabn[2u * q + 1u] = sn ? (((slo + m + 1u) << 16) | (sn - m - 1u)) : (slo << 16);
+    }
+    if (kCta) {
+        if (tid < 8u) { C.steam[tid].kmin = 0xffffffffu; C.steam[tid].kmax = 0u; C.steam[tid].lcnt = 0u; }
+        if (tid < 192u) C.sbins[tid] = 0u;
+        __syncthreads();
+    } else {
+        __syncwarp();
+    }
+}
+
+// Thread levels (P = 8 or 4): a thread owns 8 / P whole sub-ranges; the ranks of a sub-range's free elements
+// among themselves are their new positions (the reference's sort of the first n-1, done by counting).
+template <int LOGP>
+__device__ __forceinline__ void sub_thread_level(const SubCtx& C, int j, int axis) {
+    constexpr int P = 1 << LOGP, G = 8 / P;
+    const unsigned tid = threadIdx.x, nsub = 1u << j;
+    const unsigned* tab = C.stab + (j & 1) * (kFinishT / 2);
+    unsigned* tabn = C.stab + ((j + 1) & 1) * (kFinishT / 2);
+    const float* __restrict__ kcol = C.ncol ? C.scol + (size_t)axis * kSubTS : nullptr;
+    unsigned long long comp[8];
+    unsigned slot[8], rank[8], glo[G], gn[G];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        const unsigned q = tid * G + g;
+        const unsigned ent = q < nsub ? tab[q] : 0u;
+        glo[g] = ent >> 16;
+        gn[g] = ent & 0xffffu;
+        if (q < nsub) {
+            const unsigned sn = gn[g], m = sn >> 1;
+            tabn[2u * q] = (glo[g] << 16) | m;
+            tabn[2u * q + 1u] = sn ? (((glo[g] + m + 1u) << 16) | (sn - m - 1u)) : (glo[g] << 16);
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        const unsigned sn = gn[e >> LOGP], slo = glo[e >> LOGP], i = (unsigned)(e & (P - 1));
+        comp[e] = ~0ull;
+        slot[e] = 0u;
+        rank[e] = 0u;
+        if (sn >= 3u && i + 1u < sn) {
+            const unsigned s = C.sord[slo + i];
+            const unsigned id = (unsigned)C.sidx[s];
+            const float f = kcol ? kcol[s] : C.pts[(size_t)id * C.dim + axis];
+            comp[e] = composite(ordered_key(f), id);
+            slot[e] = s;
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e)
+#pragma unroll
+        for (int f = e + 1; f < 8; ++f)
+            if ((e >> LOGP) == (f >> LOGP)) {   // same sub-range (padding is larger than every element)
+                const unsigned lt = comp[f] < comp[e] ? 1u : 0u;
+                rank[e] += lt;
+                rank[f] += 1u - lt;
+            }
+#pragma unroll
+    for (int e = 0; e < 8; ++e)
+        if (comp[e] != ~0ull) C.sord[glo[e >> LOGP] + rank[e]] = (unsigned short)slot[e];
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(kSubBlock, 2) k_subtree(Cols src, int ncol, const float* __restrict__ pts, int dim,
+                                                          unsigned N, int level, int depth0, OutPtrs out,
+                                                          unsigned out_lo, int* err) {
     extern __shared__ __align__(16) unsigned char smem[];
-    constexpr int T = kFinishT;
     unsigned lo, n;
     seg_range(N, level, blockIdx.x, lo, n);
     if (n == 0) return;
-    constexpr int TS = kFinishT + 8;  // column stride: the staged window starts at a 16-byte aligned element
-    float* scol = reinterpret_cast<float*>(smem);                         // [ncol][TS] coordinates by slot
-    int32_t* sidx = reinterpret_cast<int32_t*>(scol + (size_t)ncol * TS); // [TS]       point index by slot
-    unsigned* xkey = reinterpret_cast<unsigned*>(sidx + TS);              // [T]        exchange buffer (keys)
-    unsigned* stab = xkey + T;                                            // [T/2]      sub-range table (lo << 16 | n)
-    unsigned short* sord = reinterpret_cast<unsigned short*>(stab + T / 2);  // [T]     slot by position
-    unsigned short* xslot = sord + T;                                     // [T]        exchange buffer (slots)
+    SubCtx C;
+    C.scol = reinterpret_cast<float*>(smem);
+    C.sidx = reinterpret_cast<int32_t*>(C.scol + (size_t)ncol * kSubTS);
+    C.slist = reinterpret_cast<unsigned long long*>(C.sidx + kSubTS);
+    C.steam = reinterpret_cast<SubTeam*>(C.slist + (size_t)kSubWarps * kSubWarpScratch);
+    C.sbins = reinterpret_cast<unsigned*>(C.steam + 8);
+    C.swtot = C.sbins + 192;
+    C.stab = C.swtot + kSubWarps;
+    C.sord = reinterpret_cast<unsigned short*>(C.stab + kFinishT);
+    C.pts = pts;
+    C.ncol = ncol;
+    C.dim = dim;
+    C.err = err;
     __shared__ __align__(8) unsigned long long fin_bar;
     const unsigned tid = threadIdx.x;
     // Stage the window with the TMA engine: one bulk copy per column (cp.async.bulk, completion counted in
@@ -865,140 +1151,45 @@ __global__ void __launch_bounds__(kFinishBlock, 2) k_finish(Cols src, int ncol, 
     __syncthreads();
     if (tid == 0) {
         mbar_expect_tx(&fin_bar, bytes * (unsigned)(ncol + 1));
-        for (int c = 0; c < ncol; ++c) tma_load_1d(scol + c * TS, src.c[c] + alo, bytes, &fin_bar);
-        tma_load_1d(sidx, src.idx + alo, bytes, &fin_bar);
+        for (int c = 0; c < ncol; ++c) tma_load_1d(C.scol + (size_t)c * kSubTS, src.c[c] + alo, bytes, &fin_bar);
+        tma_load_1d(C.sidx, src.idx + alo, bytes, &fin_bar);
     }
-    for (unsigned p = tid; p < n; p += kFinishBlock) sord[p] = (unsigned short)(p + delta);
+    for (unsigned p = tid; p < n; p += kSubBlock) C.sord[p] = (unsigned short)(p + delta);
+    if (tid < 8u) { C.steam[tid].kmin = 0xffffffffu; C.steam[tid].kmax = 0u; C.steam[tid].lcnt = 0u; }
+    if (tid < 192u) C.sbins[tid] = 0u;
+    if (tid == 0) C.stab[0] = n;   // sub-range 0 of sub-level 0: lo = 0, size n
     if (!__syncthreads_and(mbar_wait(&fin_bar, 0) ? 1 : 0)) {  // never expected; same data through the LSU instead
-        for (unsigned p = tid; p < n; p += kFinishBlock) {
-            sidx[delta + p] = src.idx[lo + p];
-            for (int c = 0; c < ncol; ++c) scol[c * TS + delta + p] = src.c[c][lo + p];
+        for (unsigned p = tid; p < n; p += kSubBlock) {
+            C.sidx[delta + p] = src.idx[lo + p];
+            for (int c = 0; c < ncol; ++c) C.scol[(size_t)c * kSubTS + delta + p] = src.c[c][lo + p];
         }
+        __syncthreads();
     }
-    if (tid == 0) stab[0] = n;  // sub-range 0 of sub-level 0: lo = 0, size n
+    int logP0 = 3;
+    while ((1u << logP0) < n) ++logP0;
+    int j = 0;
+    const int d0 = depth0 + level;
+    for (; (n >> j) >= 3u && logP0 - j >= 9; ++j) sub_team_level<true>(C, j, logP0 - j, (d0 + j) % dim);
+    // from here on every warp owns its sub-ranges: no CTA-wide barrier until the write-out
+    for (; (n >> j) >= 3u; ++j) {
+        const int logP = logP0 - j, axis = (d0 + j) % dim;
+        if (logP >= 4) sub_team_level<false>(C, j, logP, axis);
+        else if (logP == 3) sub_thread_level<3>(C, j, axis);
+        else sub_thread_level<2>(C, j, axis);
+    }
     __syncthreads();
-    // The first `skip` sub-levels of this range were already split by the select/partition kernels: only
-    // walk the table down, and mark their node slots (already final in the tree arrays) as not ours.
-    for (int j = 0; j < skip; ++j) {
-        const unsigned nsub = 1u << j;
-        unsigned ent[2];
-        int cnt = 0;
-        for (unsigned q = tid; q < nsub; q += kFinishBlock) ent[cnt++] = stab[q];
-        __syncthreads();
-        cnt = 0;
-        for (unsigned q = tid; q < nsub; q += kFinishBlock) {
-            const unsigned tb = ent[cnt++];
-            const unsigned sn = tb & 0xffffu, slo = tb >> 16, m = sn >> 1;
-            if (sn) sord[slo + m] = (unsigned short)kInfSlot;
-            stab[2 * q] = (slo << 16) | m;
-            stab[2 * q + 1] = sn ? (((slo + m + 1u) << 16) | (sn - m - 1u)) : (slo << 16);
-        }
-        __syncthreads();
-    }
-    const unsigned vbase = tid * 8u;
-    for (int j = skip; (n >> j) >= 3u; ++j) {
-        const unsigned nsub = 1u << j;
-        const int axis = (depth0 + level + j) % dim;
-        const unsigned maxsort = (n >> j) - 1u;  // the left-most sub-range is the largest
-        unsigned P = 2;
-        int logP = 1;
-        while (P < maxsort) { P <<= 1; ++logP; }
-        unsigned key[8], idx[8], slot[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            const unsigned v = vbase + e, sub = v >> logP, i = v & (P - 1u);
-            const unsigned tb = sub < nsub ? stab[sub] : 0u;
-            const unsigned sn = tb & 0xffffu, slo = tb >> 16;
-            key[e] = kInfKey;
-            idx[e] = 0xffffffffu;
-            slot[e] = kInfSlot;
-            if (sn >= 3u && i + 1u < sn) {  // position i of the sub-range's first n-1 (the last slot is pinned)
-                slot[e] = sord[slo + i];
-                idx[e] = (unsigned)sidx[slot[e]];
-                const float f = ncol ? scol[axis * TS + slot[e]] : pts[(size_t)idx[e] * dim + axis];
-                key[e] = ordered_key(f);
-            }
-        }
-        for (unsigned k = 2; k <= P; k <<= 1) {
-            const bool last = k == P;  // the final merge of every sub-range is ascending
-            unsigned s = k >> 1;
-            for (; s >= 256u; s >>= 1) {  // partner in another warp: through shared memory (keys+slots, then indices)
-                const unsigned d = s >> 3, pt = tid ^ d;
-                const bool keep_min = ((tid & d) == 0u) == (last || ((vbase & k) == 0u));
-                unsigned ok[8], os[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) { xkey[e * kFinishBlock + tid] = key[e]; xslot[e * kFinishBlock + tid] = (unsigned short)slot[e]; }
-                __syncthreads();
-#pragma unroll
-                for (int e = 0; e < 8; ++e) { ok[e] = xkey[e * kFinishBlock + pt]; os[e] = xslot[e * kFinishBlock + pt]; }
-                __syncthreads();
-#pragma unroll
-                for (int e = 0; e < 8; ++e) xkey[e * kFinishBlock + tid] = idx[e];
-                __syncthreads();
-#pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const unsigned oi = xkey[e * kFinishBlock + pt];
-                    fin_ce_partner(key[e], idx[e], slot[e], ok[e], oi, os[e], keep_min);
-                }
-                __syncthreads();
-            }
-            for (; s >= 8u; s >>= 1) {  // partner in the same warp
-                const unsigned d = s >> 3;
-                const bool keep_min = ((tid & d) == 0u) == (last || ((vbase & k) == 0u));
-#pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const unsigned ok = __shfl_xor_sync(0xffffffffu, key[e], d);
-                    const unsigned oi = __shfl_xor_sync(0xffffffffu, idx[e], d);
-                    const unsigned os = __shfl_xor_sync(0xffffffffu, slot[e], d);
-                    fin_ce_partner(key[e], idx[e], slot[e], ok, oi, os, keep_min);
-                }
-            }
-            if (s == 4u) { fin_reg_step<4>(key, idx, slot, vbase, k, last); s = 2u; }
-            if (s == 2u) { fin_reg_step<2>(key, idx, slot, vbase, k, last); s = 1u; }
-            fin_reg_step<1>(key, idx, slot, vbase, k, last);
-        }
-        // sorted elements go back to the positions this thread's virtual slots stand for (padding has sunk
-        // to the end of every sub-range's block and is dropped)
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            const unsigned v = vbase + e, sub = v >> logP, i = v & (P - 1u);
-            const unsigned tb = sub < nsub ? stab[sub] : 0u;
-            const unsigned sn = tb & 0xffffu, slo = tb >> 16;
-            if (sn >= 3u && i + 1u < sn) sord[slo + i] = (unsigned short)slot[e];
-        }
-        // next sub-level's table: range s -> 2s (left n/2) and 2s+1 (right n-n/2-1), the node slot drops out
-        if ((n >> (j + 1)) >= 3u) {
-            unsigned ent[2];
-            int cnt = 0;
-            for (unsigned q = tid; q < nsub; q += kFinishBlock) ent[cnt++] = stab[q];
-            __syncthreads();
-            cnt = 0;
-            for (unsigned q = tid; q < nsub; q += kFinishBlock) {
-                const unsigned tb = ent[cnt++];
-                const unsigned sn = tb & 0xffffu, slo = tb >> 16, m = sn >> 1;
-                stab[2 * q] = (slo << 16) | m;
-                stab[2 * q + 1] = sn ? (((slo + m + 1u) << 16) | (sn - m - 1u)) : (slo << 16);
-            }
-        }
-        __syncthreads();
-    }
     // Every replica of the tree arrays receives this window: the sub-tree all-gather is fused into the store.
     // Both arrays are written as flat runs (consecutive threads -> consecutive 4-byte words), so a warp emits
-    // whole 128-byte lines, which is what NVLink wants for the remote replicas.  Slots of nodes placed by
-    // earlier levels are skipped (they already hold their final value everywhere).
+    // whole 128-byte lines, which is what NVLink wants for the remote replicas.
     const unsigned total = ncol ? n * (unsigned)dim : 0u;
     for (int r = 0; r < out.n; ++r) {
         int32_t* __restrict__ perm = out.perm[r] + out_lo + lo;
         float* __restrict__ tree_pts = out.tp[r] ? out.tp[r] + (size_t)(out_lo + lo) * dim : nullptr;
-        for (unsigned p = tid; p < n; p += kFinishBlock) {
-            const unsigned slot = sord[p];
-            if (slot != kInfSlot) perm[p] = sidx[slot];
-        }
+        for (unsigned p = tid; p < n; p += kSubBlock) perm[p] = C.sidx[C.sord[p]];
         if (tree_pts) {
-            for (unsigned f = tid; f < total; f += kFinishBlock) {
+            for (unsigned f = tid; f < total; f += kSubBlock) {
                 const unsigned p = f / (unsigned)dim, c = f - p * (unsigned)dim;
-                const unsigned slot = sord[p];
-                if (slot != kInfSlot) tree_pts[f] = scol[c * TS + slot];
+                tree_pts[f] = C.scol[(size_t)c * kSubTS + C.sord[p]];
             }
         }
     }
@@ -1063,41 +1254,45 @@ static inline int ctas_per_seg(int64_t nseg, int64_t seg_n, int64_t min_chunk) {
         if (e_ != cudaSuccess) return fail(std::string(what) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
+// Opt-in shared-memory sizes are a property of the (function, device) pair: set them once per device, not per build.
+static int set_func_attributes_once() {
+    static std::mutex mu;
+    static bool done[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail(std::string("kd build: cudaGetDevice: ") + cudaGetErrorString(e));
+    std::lock_guard<std::mutex> lock(mu);
+    if (dev >= 0 && dev < 64 && done[dev]) return 0;
+    e = cudaFuncSetAttribute(k_subtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)subtree_smem_bytes(kMaxCarry));
+#define KD_MED_ATTR(NC) if (e == cudaSuccess) e = cudaFuncSetAttribute(k_medium<NC, 11>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)medium_smem_bytes())
+    KD_MED_ATTR(0); KD_MED_ATTR(1); KD_MED_ATTR(2); KD_MED_ATTR(3); KD_MED_ATTR(4);
+    KD_MED_ATTR(5); KD_MED_ATTR(6); KD_MED_ATTR(7); KD_MED_ATTR(8);
+#undef KD_MED_ATTR
+    if (e != cudaSuccess) return fail(std::string("kd build: cudaFuncSetAttribute: ") + cudaGetErrorString(e));
+    if (dev >= 0 && dev < 64) done[dev] = true;
+    return 0;
+}
+
 // Builds the sub-tree of one range whose points already sit in buf[cur] (slots 0..n-1): select/partition
-// levels, then the finisher.  `depth0` is the depth of the range's node in the whole tree (it fixes the
+// levels, then the shared-memory sub-tree builder.  `depth0` is the depth of the range's node in the whole tree (it fixes the
 // split axes), `out_lo` the slot of the range's first point in the tree arrays, `out` every replica of
 // the tree arrays that receives the result.
 int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, unsigned out_lo, OutPtrs out,
                const float* points, BuildScratch sc, cudaStream_t stream) {
-    const size_t fin_smem = finish_smem_bytes(ncol);
-    {
-        cudaError_t e = cudaFuncSetAttribute(k_finish, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)finish_smem_bytes(kMaxCarry));
-        if (e != cudaSuccess) return fail(std::string("kd build: cudaFuncSetAttribute: ") + cudaGetErrorString(e));
-    }
+    if (int rc = set_func_attributes_once()) return rc;
+    const size_t sub_smem = subtree_smem_bytes(ncol);
     const unsigned N = (unsigned)n;
     // Level schedule: select/partition with several CTAs per range while ranges are large, one CTA per
-    // range (k_medium) while they exceed kFinishEff, then the shared-memory finisher.  A finisher CTA
-    // always works on a window of up to kFinishT slots, i.e. on the ancestor `skip` levels up.
+    // range (k_medium) while they exceed kFinishT, then the shared-memory sub-tree builder takes every
+    // range of that level down to its leaves.
     int finish_level = 0;
-    while ((n >> finish_level) > kFinishEff) ++finish_level;
-    int skip = 0;
-    while (skip < finish_level && (n >> (finish_level - skip - 1)) <= kFinishT) ++skip;
-    {
-        cudaError_t e = cudaSuccess;
-#define KD_MED_ATTR(NC) if (e == cudaSuccess) e = cudaFuncSetAttribute(k_medium<NC, 11>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)medium_smem_bytes())
-        KD_MED_ATTR(0); KD_MED_ATTR(1); KD_MED_ATTR(2); KD_MED_ATTR(3); KD_MED_ATTR(4);
-        KD_MED_ATTR(5); KD_MED_ATTR(6); KD_MED_ATTR(7); KD_MED_ATTR(8);
-#undef KD_MED_ATTR
-        if (e != cudaSuccess) return fail(std::string("kd build: cudaFuncSetAttribute: ") + cudaGetErrorString(e));
-    }
+    while ((n >> finish_level) > kFinishT) ++finish_level;
     for (int level = 0;; ++level) {
         const int64_t nseg = 1ll << level;
         if (level == finish_level) {
-            k_finish<<<(unsigned)(nseg >> skip), kFinishBlock, fin_smem, stream>>>(buf[cur], ncol, points, dim, N,
-                                                                                  level - skip, depth0, out, out_lo,
-                                                                                  skip);
-            KD_LAUNCH_CHECK("k_finish");
+            k_subtree<<<(unsigned)nseg, kSubBlock, sub_smem, stream>>>(buf[cur], ncol, points, dim, N, level, depth0,
+                                                                       out, out_lo, sc.err);
+            KD_LAUNCH_CHECK("k_subtree");
             break;
         }
         if ((n >> level) <= kMediumMax) {

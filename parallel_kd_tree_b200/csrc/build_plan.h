@@ -7,8 +7,7 @@ namespace kd {
 
 constexpr int kMaxCarry = 8;      // dim <= kMaxCarry: coordinates travel with the points (SoA columns);
                                   // larger dim: only indices move and keys are gathered per level
-constexpr int kFinishT = 4096;    // ranges of at most this many points are finished in shared memory
-constexpr int kFinishEff = 512;     // select/partition levels go on until ranges have at most this many points
+constexpr int kFinishT = 4096;    // ranges of at most this many points are finished in shared memory (k_subtree)
 constexpr int kMediumMax = 16384;   // ranges up to this size are handled by one CTA per level (k_medium)
 constexpr int kTargetCtas = 148 * 16;
 
@@ -86,9 +85,11 @@ void reset_launches();
 
 inline size_t medium_smem_bytes() { return (size_t)kMediumMax * 4 + (size_t)2048 * 4; }
 
-inline size_t finish_smem_bytes(int ncol) {
-    // scol[ncol][T+8] f32, sidx[T+8] i32, xkey[T] u32, stab[T/2] u32, sord[T] u16, xslot[T] u16
-    return (size_t)(ncol + 1) * (kFinishT + 8) * 4 + (size_t)kFinishT * 4 + (size_t)kFinishT * 2 + (size_t)kFinishT * 2 * 2;
+inline size_t subtree_smem_bytes(int ncol) {
+    // scol[ncol][T+8] f32, sidx[T+8] i32, slist[16 warps][160] u64, steam[8] x 16 B, sbins[192] u32, swtot[16] u32,
+    // stab[2][T/2] u32, sord[T] u16  (k_subtree carves them in this order)
+    return (size_t)(ncol + 1) * (kFinishT + 8) * 4 + (size_t)16 * 160 * 8 + 8 * 16 + 192 * 4 + 16 * 4 +
+           (size_t)kFinishT * 4 + (size_t)kFinishT * 2;
 }
 
 }  // namespace kd

@@ -20,8 +20,9 @@ def _compare(kd, pts, what):
     assert torch.equal(tree_pts.cpu(), pts[cpu_perm.long()]), f"{what}: tree_points != points[perm]"
 
 
-@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 31, 100, 1000, 4095, 4096])
-@pytest.mark.parametrize("dim", [1, 2, 3, 4])
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 6, 7, 8, 9, 15, 16, 17, 31, 33, 63, 64, 65, 100, 127, 129, 255, 257, 511,
+                               513, 1000, 1023, 1025, 2047, 2049, 3000, 4095, 4096])
+@pytest.mark.parametrize("dim", [1, 2, 3, 4, 8])
 def test_finisher_only_sizes(kd, n, dim):
     pts, _ = kd.ops.generate_problem(n + dim, dim, n, 0)
     _compare(kd, pts, f"n={n} dim={dim}")
@@ -48,6 +49,13 @@ def test_heavy_ties_and_signed_zero(kd):
         _compare(kd, pts, f"ties n={n} dim={dim}")
     pts = torch.zeros(20000, 3)           # every key equal: all six digit passes, pure index order
     _compare(kd, pts, "all-equal")
+    for n in (7, 100, 1000, 4096):        # the same inside the shared-memory sub-tree builder (index digits only)
+        _compare(kd, torch.zeros(n, 2), f"all-equal n={n}")
+        pts = torch.randint(-2, 3, (n, 3), generator=g).float()
+        _compare(kd, pts, f"ties n={n}")
+    pts = torch.tensor([0.0, 1e-30, -1e-30, 1.0, -1.0, 3e38, -3e38, 1e-38]).repeat(500)[:, None].repeat(1, 2)
+    pts = pts + torch.arange(pts.shape[0])[:, None] * 0.0   # wide exponent range across zero
+    _compare(kd, pts[torch.randperm(pts.shape[0], generator=g)], "wide-range")
 
 
 def test_clustered(kd):
