@@ -24,6 +24,7 @@
 #include <algorithm>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 #include <string>
 
@@ -871,7 +872,9 @@ __device__ __forceinline__ void sub_team_level(const SubCtx& C, int j, int logP,
     const unsigned* tab = C.stab + (j & 1) * (kFinishT / 2);
     unsigned* tabn = C.stab + ((j + 1) & 1) * (kFinishT / 2);
     const bool in_range = q < (1u << j);
-    const unsigned ent = in_range ? tab[q] : 0u;
+    // table slot of sub-range q = its first virtual position / 4: the slots of a warp's sub-ranges are then private
+    // to the warp at every level (warps run unsynchronised below P = 512)
+    const unsigned ent = in_range ? tab[q << (logP - 2)] : 0u;
     const unsigned slo = ent >> 16, sn = ent & 0xffffu, m = sn >> 1;
     bool active = sn >= 3u;
     const unsigned tmask = (kCta || tpt == 32u) ? FULL : (((1u << tpt) - 1u) << (lane & ~(tpt - 1u)));
@@ -1056,8 +1059,8 @@ __device__ __forceinline__ void sub_team_level(const SubCtx& C, int j, int logP,
             C.sord[slo + pos] = (unsigned short)slot[e];
         }
     if (in_range && tl == 0) {
-        tabn[2u * q] = (slo << 16) | m;
-        tabn[2u * q + 1u] = sn ? (((slo + m + 1u) << 16) | (sn - m - 1u)) : (slo << 16);
+        tabn[(2u * q) << (logP - 3)] = (slo << 16) | m;
+        tabn[(2u * q + 1u) << (logP - 3)] = sn ? (((slo + m + 1u) << 16) | (sn - m - 1u)) : (slo << 16);
     }
     if (kCta) {
         if (tid < 8u) { C.steam[tid].kmin = 0xffffffffu; C.steam[tid].kmax = 0u; C.steam[tid].lcnt = 0u; }
@@ -1082,10 +1085,10 @@ __device__ __forceinline__ void sub_thread_level(const SubCtx& C, int j, int axi
 #pragma unroll
     for (int g = 0; g < G; ++g) {
         const unsigned q = tid * G + g;
-        const unsigned ent = q < nsub ? tab[q] : 0u;
+        const unsigned ent = q < nsub ? tab[q << (LOGP - 2)] : 0u;
         glo[g] = ent >> 16;
         gn[g] = ent & 0xffffu;
-        if (q < nsub) {
+        if (LOGP == 3 && q < nsub) {   // (the children of a P = 4 level are never looked up)
             const unsigned sn = gn[g], m = sn >> 1;
             tabn[2u * q] = (glo[g] << 16) | m;
             tabn[2u * q + 1u] = sn ? (((glo[g] + m + 1u) << 16) | (sn - m - 1u)) : (glo[g] << 16);
@@ -1122,7 +1125,7 @@ __device__ __forceinline__ void sub_thread_level(const SubCtx& C, int j, int axi
 
 __global__ void __launch_bounds__(kSubBlock, 2) k_subtree(Cols src, int ncol, const float* __restrict__ pts, int dim,
                                                           unsigned N, int level, int depth0, OutPtrs out,
-                                                          unsigned out_lo, int* err) {
+                                                          unsigned out_lo, int* err, int max_levels) {
     extern __shared__ __align__(16) unsigned char smem[];
     unsigned lo, n;
     seg_range(N, level, blockIdx.x, lo, n);
@@ -1169,9 +1172,9 @@ __global__ void __launch_bounds__(kSubBlock, 2) k_subtree(Cols src, int ncol, co
     while ((1u << logP0) < n) ++logP0;
     int j = 0;
     const int d0 = depth0 + level;
-    for (; (n >> j) >= 3u && logP0 - j >= 9; ++j) sub_team_level<true>(C, j, logP0 - j, (d0 + j) % dim);
+    for (; (n >> j) >= 3u && logP0 - j >= 9 && j < max_levels; ++j) sub_team_level<true>(C, j, logP0 - j, (d0 + j) % dim);
     // from here on every warp owns its sub-ranges: no CTA-wide barrier until the write-out
-    for (; (n >> j) >= 3u; ++j) {
+    for (; (n >> j) >= 3u && j < max_levels; ++j) {   // (max_levels: debugging aid, KD_B200_SUBTREE_MAXLEVELS)
         const int logP = logP0 - j, axis = (d0 + j) % dim;
         if (logP >= 4) sub_team_level<false>(C, j, logP, axis);
         else if (logP == 3) sub_thread_level<3>(C, j, axis);
@@ -1254,6 +1257,11 @@ static inline int ctas_per_seg(int64_t nseg, int64_t seg_n, int64_t min_chunk) {
         if (e_ != cudaSuccess) return fail(std::string(what) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
+static int subtree_max_levels() {
+    static const int v = [] { const char* e = std::getenv("KD_B200_SUBTREE_MAXLEVELS"); return e ? std::atoi(e) : 64; }();
+    return v;
+}
+
 // Opt-in shared-memory sizes are a property of the (function, device) pair: set them once per device, not per build.
 static int set_func_attributes_once() {
     static std::mutex mu;
@@ -1291,7 +1299,7 @@ int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, u
         const int64_t nseg = 1ll << level;
         if (level == finish_level) {
             k_subtree<<<(unsigned)nseg, kSubBlock, sub_smem, stream>>>(buf[cur], ncol, points, dim, N, level, depth0,
-                                                                       out, out_lo, sc.err);
+                                                                       out, out_lo, sc.err, subtree_max_levels());
             KD_LAUNCH_CHECK("k_subtree");
             break;
         }
