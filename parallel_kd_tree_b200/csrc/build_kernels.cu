@@ -862,6 +862,28 @@ __device__ __forceinline__ void sub_load(const SubCtx& C, int axis, unsigned slo
     }
 }
 
+// Team-wide reductions.  Multi-warp teams (kCta) reduce per warp here and meet in shared memory afterwards;
+// sub-warp teams are aligned groups of tpt lanes: xor butterflies (a REDUX with a per-lane member mask would
+// be emulated with a loop), whole-warp teams use one REDUX.
+template <bool kCta>
+__device__ __forceinline__ unsigned team_add(unsigned v, unsigned tpt) {
+    if (kCta || tpt == 32u) return __reduce_add_sync(0xffffffffu, v);
+    for (unsigned o = tpt >> 1; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+template <bool kCta>
+__device__ __forceinline__ unsigned team_min(unsigned v, unsigned tpt) {
+    if (kCta || tpt == 32u) return __reduce_min_sync(0xffffffffu, v);
+    for (unsigned o = tpt >> 1; o; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+template <bool kCta>
+__device__ __forceinline__ unsigned team_max(unsigned v, unsigned tpt) {
+    if (kCta || tpt == 32u) return __reduce_max_sync(0xffffffffu, v);
+    for (unsigned o = tpt >> 1; o; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
 // Team levels.  kCta: the team spans whole warps (P >= 512); otherwise it is an aligned group of lanes.
 template <bool kCta>
 __device__ __forceinline__ void sub_team_level(const SubCtx& C, int j, int logP, int axis) {
@@ -895,8 +917,8 @@ __device__ __forceinline__ void sub_team_level(const SubCtx& C, int j, int logP,
 #pragma unroll
     for (int e = 0; e < 8; ++e)
         if ((valid >> e) & 1u) { const unsigned k = (unsigned)(comp[e] >> 32); kmn = min(kmn, k); kmx = max(kmx, k); }
-    kmn = __reduce_min_sync(tmask, kmn);
-    kmx = __reduce_max_sync(tmask, kmx);
+    kmn = team_min<kCta>(kmn, tpt);
+    kmx = team_max<kCta>(kmx, tpt);
     if (kCta) {
         SubTeam& T = C.steam[q];
         if (lane == 0 && kmn <= kmx) { atomicMin(&T.kmin, kmn); atomicMax(&T.kmax, kmx); }
@@ -919,6 +941,8 @@ __device__ __forceinline__ void sub_team_level(const SubCtx& C, int j, int logP,
         const bool need = active && acnt > lcap;
         if (kCta) { if (!__syncthreads_or(need ? 1 : 0)) break; }
         else if (!__any_sync(FULL, need)) break;
+        // per-thread counts: sixteen 4-bit fields; digit d lives in the low (d < 8) or high nibble of byte d & 7,
+        // so that the two nibble planes are bins 0..7 and 8..15 in order
         unsigned long long acc = 0ull;
         unsigned dig = 0u;
         if (need) {
@@ -926,16 +950,19 @@ __device__ __forceinline__ void sub_team_level(const SubCtx& C, int j, int logP,
             for (int e = 0; e < 8; ++e) {
                 const unsigned u = mode ? (unsigned)comp[e] : (unsigned)(comp[e] >> 32) - base;
                 const unsigned d = (u >> sh) & 15u;
-                if ((alive >> e) & 1u) { acc += 1ull << (4u * d); dig |= d << (4 * e); }
+                if ((alive >> e) & 1u) { acc += 1ull << (((d & 7u) << 3) | ((d >> 3) << 2)); dig |= d << (4 * e); }
             }
         }
-        unsigned w[8];   // word k: bins 2k (low half) and 2k+1 (high half)
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const unsigned byte = (unsigned)(acc >> (8 * k)) & 0xffu;
-            w[k] = __reduce_add_sync(tmask, (byte & 15u) | ((byte >> 4) << 16));
-        }
+        const unsigned long long pa = acc & 0x0f0f0f0f0f0f0f0full, pb = (acc >> 4) & 0x0f0f0f0f0f0f0f0full;
+        unsigned tb = 16u, cbase = 0u, ccnt = 0u;
         if (kCta) {
+            // counts of up to 4095: 16-bit fields, word k = bins 2k (low half) and 2k+1 (high half)
+            unsigned w[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const unsigned c16 = (unsigned)((k < 4 ? pa : pb) >> (16 * (k & 3))) & 0xffffu;
+                w[k] = __reduce_add_sync(FULL, (c16 & 0xffu) | ((c16 >> 8) << 16));
+            }
             unsigned* B = C.sbins + (it % 3u) * 64u;
             if (need && lane < 8u) {
                 unsigned v = w[0];
@@ -946,18 +973,37 @@ __device__ __forceinline__ void sub_team_level(const SubCtx& C, int j, int logP,
             if (tid < 64u) C.sbins[((it + 2u) % 3u) * 64u + tid] = 0u;   // read two barriers ago, used two from now
             __syncthreads();
             if (need) {
+                unsigned cum = 0u;
 #pragma unroll
-                for (int k = 0; k < 8; ++k) w[k] = B[q * 8u + k];
+                for (int b = 0; b < 16; ++b) {
+                    const unsigned c = (B[q * 8u + (b >> 1)] >> (16 * (b & 1))) & 0xffffu;
+                    if (tb == 16u && r < cum + c) { tb = (unsigned)b; cbase = cum; ccnt = c; }
+                    cum += c;
+                }
+            }
+        } else {
+            // at most 255 elements per team: byte fields, word k = bins 4k .. 4k+3
+            unsigned w[4] = {(unsigned)pa, (unsigned)(pa >> 32), (unsigned)pb, (unsigned)(pb >> 32)};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) w[k] = team_add<false>(w[k], tpt);
+            // inclusive byte prefixes by one multiply per word (no byte overflows: the total is below 256)
+            const unsigned p0 = w[0] * 0x01010101u, p1 = w[1] * 0x01010101u, p2 = w[2] * 0x01010101u, p3 = w[3] * 0x01010101u;
+            const unsigned c1 = p0 >> 24, c2 = c1 + (p1 >> 24), c3 = c2 + (p2 >> 24), c4 = c3 + (p3 >> 24);
+            if (r < c4) {
+                const unsigned kk = (r >= c1 ? 1u : 0u) + (r >= c2 ? 1u : 0u) + (r >= c3 ? 1u : 0u);
+                const unsigned pk = kk == 0u ? p0 : kk == 1u ? p1 : kk == 2u ? p2 : p3;
+                const unsigned wb = kk == 0u ? 0u : kk == 1u ? c1 : kk == 2u ? c2 : c3;
+                const unsigned rr = r - wb;
+                const unsigned b0 = pk & 0xffu, b1 = (pk >> 8) & 0xffu, b2 = (pk >> 16) & 0xffu, b3 = pk >> 24;
+                const unsigned bi = (rr >= b0 ? 1u : 0u) + (rr >= b1 ? 1u : 0u) + (rr >= b2 ? 1u : 0u);
+                const unsigned below = bi == 0u ? 0u : bi == 1u ? b0 : bi == 2u ? b1 : b2;
+                const unsigned upto = bi == 0u ? b0 : bi == 1u ? b1 : bi == 2u ? b2 : b3;
+                tb = 4u * kk + bi;
+                cbase = wb + below;
+                ccnt = upto - below;
             }
         }
         if (need) {
-            unsigned cum = 0u, tb = 16u, cbase = 0u, ccnt = 0u;
-#pragma unroll
-            for (int b = 0; b < 16; ++b) {
-                const unsigned c = (w[b >> 1] >> (16 * (b & 1))) & 0xffffu;
-                if (tb == 16u && r < cum + c) { tb = (unsigned)b; cbase = cum; ccnt = c; }
-                cum += c;
-            }
             if (tb == 16u) {   // the counts lost the wanted rank: internal error, leave the sub-range as it is
                 if (tl == 0) atomicExch(C.err, 40 + j);
                 active = false; alive = 0u; valid = 0u; acnt = 0u;
@@ -978,9 +1024,9 @@ __device__ __forceinline__ void sub_team_level(const SubCtx& C, int j, int logP,
     }
     // ---- the alive elements -> the team's list (ballot ranks; one atomic per warp for multi-warp teams) ----
     {
-        const unsigned total = __reduce_add_sync(tmask, (unsigned)__popc(alive));
         unsigned run = 0u;
         if (kCta) {
+            const unsigned total = __reduce_add_sync(FULL, (unsigned)__popc(alive));
             if (lane == 0 && total) run = atomicAdd(&C.steam[q].lcnt, total);
             run = __shfl_sync(FULL, run, 0);
         }
@@ -1006,6 +1052,14 @@ __device__ __forceinline__ void sub_team_level(const SubCtx& C, int j, int logP,
     tsync();
     const unsigned long long X = active ? XM[0] : 0ull;
     unsigned long long M = (active && r > 0u) ? XM[1] : 0ull;
+    // side of every element, once: bit e of lessX / isX
+    unsigned lessX = 0u, isX = 0u;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        lessX |= (comp[e] < X ? 1u : 0u) << e;
+        isX |= (comp[e] == X ? 1u : 0u) << e;
+    }
+    lessX &= valid;
     {   // the node was the smallest candidate: the left maximum is the largest element below it
         const bool needM = active && r == 0u;
         const bool anyM = kCta ? (__syncthreads_or(needM ? 1 : 0) != 0) : (__any_sync(FULL, needM) != 0);
@@ -1014,11 +1068,11 @@ __device__ __forceinline__ void sub_team_level(const SubCtx& C, int j, int logP,
             if (needM) {
 #pragma unroll
                 for (int e = 0; e < 8; ++e)
-                    if (comp[e] < X && comp[e] > best) best = comp[e];
+                    if (((lessX >> e) & 1u) && comp[e] > best) best = comp[e];
             }
-            const unsigned hk = __reduce_max_sync(tmask, (unsigned)(best >> 32));
+            const unsigned hk = team_max<kCta>((unsigned)(best >> 32), tpt);
             unsigned li = (best != 0ull && (unsigned)(best >> 32) == hk) ? (unsigned)best + 1u : 0u;
-            li = __reduce_max_sync(tmask, li);
+            li = team_max<kCta>(li, tpt);
             if (kCta) {
                 if (needM && lane == 0 && li) atomicMax(&XM[1], ((unsigned long long)hk << 32) | (li - 1u));
                 __syncthreads();
@@ -1029,14 +1083,12 @@ __device__ __forceinline__ void sub_team_level(const SubCtx& C, int j, int logP,
         }
     }
     // ---- new positions: left part (its maximum last), node, right part; the pinned element stays ----
-    unsigned cl = 0u, cr = 0u;
+    unsigned isM = 0u;
 #pragma unroll
-    for (int e = 0; e < 8; ++e)
-        if ((valid >> e) & 1u) {
-            if (comp[e] < X) cl += comp[e] != M ? 1u : 0u;
-            else if (comp[e] > X) ++cr;
-        }
-    const unsigned v = cl | (cr << 16);
+    for (int e = 0; e < 8; ++e) isM |= (comp[e] == M ? 1u : 0u) << e;
+    isM &= lessX;
+    const unsigned leftm = lessX & ~isM, rightm = valid & ~lessX & ~isX;
+    const unsigned v = (unsigned)__popc(leftm) | ((unsigned)__popc(rightm) << 16);
     unsigned incl = v;
     const unsigned sw = kCta ? 32u : tpt;
     for (unsigned o = 1; o < sw; o <<= 1) {
@@ -1049,13 +1101,13 @@ __device__ __forceinline__ void sub_team_level(const SubCtx& C, int j, int logP,
         __syncthreads();
         for (unsigned w2 = team_w0; w2 < warp; ++w2) ex += C.swtot[w2];
     }
-    unsigned exL = ex & 0xffffu, exR = ex >> 16;
+    unsigned exL = ex & 0xffffu, exR = (ex >> 16) + m + 1u;
 #pragma unroll
     for (int e = 0; e < 8; ++e)
         if ((valid >> e) & 1u) {
             unsigned pos;
-            if (comp[e] < X) pos = comp[e] == M ? m - 1u : exL++;
-            else pos = comp[e] == X ? m : m + 1u + exR++;
+            if ((lessX >> e) & 1u) pos = ((isM >> e) & 1u) ? m - 1u : exL++;
+            else pos = ((isX >> e) & 1u) ? m : exR++;
             C.sord[slo + pos] = (unsigned short)slot[e];
         }
     if (in_range && tl == 0) {
