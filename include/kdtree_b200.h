@@ -10,8 +10,9 @@
  *     right = [lo+n/2+1, lo+n)  (shape rule of kdtree_sequential.cpp:51-56);
  *   - device entry points take raw device pointers and a cudaStream_t passed as
  *     void*; they never allocate: scratch comes from the caller (sizes from the
- *     *_workspace_bytes functions) and they do not synchronise the stream
- *     unless stated.
+ *     *_workspace_bytes functions) or, for kd_build_gpu_noalloc only, from an
+ *     array built into the library; they do not synchronise the stream unless
+ *     stated.
  */
 #ifndef KDTREE_B200_H_
 #define KDTREE_B200_H_
@@ -79,6 +80,10 @@ int kd_build_gpu(const float* points, int64_t n, int dim, int32_t* perm, float* 
  * the array's address; make it before any stream capture.  Every GPU that loads the library holds the 16 MiB
  * until exit.  No counterpart in the reference. */
 int kd_build_gpu_noalloc(const float* points, int64_t n, int dim, int32_t* perm, float* tree_points, void* stream);
+/* kd_build_status for the built-in scratch: synchronises the stream and reports a device-side failure of the last
+ * kd_build_gpu_noalloc(n, dim) on the current device (that caller has no workspace pointer to pass).  Allocates
+ * nothing.  No counterpart in the reference. */
+int kd_build_status_noalloc(int64_t n, int dim, void* stream);
 /* synchronises the stream and reports a device-side failure of the last build that used `workspace` */
 int kd_build_status(const void* workspace, int64_t n, int dim, void* stream);
 /* number of kernel launches issued by the last kd_build_gpu call on this thread */

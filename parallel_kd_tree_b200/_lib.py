@@ -50,6 +50,7 @@ def _declare(lib):
         "kd_build_workspace_bytes": (C.c_size_t, [i64, i32]),
         "kd_build_gpu": (i32, [vp, i64, i32, vp, vp, vp, C.c_size_t, vp]),
         "kd_build_gpu_noalloc": (i32, [vp, i64, i32, vp, vp, vp]),
+        "kd_build_status_noalloc": (i32, [i64, i32, vp]),
         "kd_build_status": (i32, [vp, i64, i32, vp]),
         "kd_last_launch_count": (i64, []),
         "kd_nearest_gpu": (i32, [vp, vp, i64, i32, vp, i64, vp, vp, vp, vp, vp]),

@@ -1200,7 +1200,9 @@ __global__ void __launch_bounds__(kSubBlock, 2) k_subtree(Cols src, int ncol, co
     // Stage the window with the TMA engine: one bulk copy per column (cp.async.bulk, completion counted in
     // bytes on an mbarrier) instead of 512 threads issuing scalar loads.  Bulk copies need 16-byte aligned
     // addresses and sizes, so the copy starts `delta` elements early and slots are offsets into that window.
-    const unsigned delta = lo & 3u, alo = lo - delta;
+    // (all columns share one alignment phase: their bases are 256-byte aligned plus a common element offset)
+    const unsigned delta = (unsigned)((reinterpret_cast<uintptr_t>(src.idx + lo) >> 2) & 3u);
+    const ptrdiff_t alo = (ptrdiff_t)lo - (ptrdiff_t)delta;
     const unsigned bytes = ((delta + n + 3u) & ~3u) * 4u;
     if (tid == 0) mbar_init(&fin_bar, 1);
     __syncthreads();
@@ -1338,7 +1340,7 @@ static int set_func_attributes_once() {
 // split axes), `out_lo` the slot of the range's first point in the tree arrays, `out` every replica of
 // the tree arrays that receives the result.
 int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, unsigned out_lo, OutPtrs out,
-               const float* points, BuildScratch sc, cudaStream_t stream) {
+               const float* points, BuildScratch sc, cudaStream_t stream, int stop_level, int* cur_out) {
     if (int rc = set_func_attributes_once()) return rc;
     const size_t sub_smem = subtree_smem_bytes(ncol);
     const unsigned N = (unsigned)n;
@@ -1349,6 +1351,10 @@ int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, u
     while ((n >> finish_level) > kFinishT) ++finish_level;
     for (int level = 0;; ++level) {
         const int64_t nseg = 1ll << level;
+        if (level == stop_level) {   // the caller continues range by range (build_core on every range of this level)
+            if (cur_out) *cur_out = cur;
+            return 0;
+        }
         if (level == finish_level) {
             k_subtree<<<(unsigned)nseg, kSubBlock, sub_smem, stream>>>(buf[cur], ncol, points, dim, N, level, depth0,
                                                                        out, out_lo, sc.err, subtree_max_levels());
@@ -1490,7 +1496,7 @@ int build_gpu(const float* points, int64_t n, int dim, int32_t* perm, float* tre
     out.n = 1;
     out.perm[0] = perm;
     out.tp[0] = tree_points;
-    if (int rc = build_core(buf, 0, n, dim, p.ncol, 0, 0u, out, points, sc, stream)) return rc;
+    if (int rc = build_core(buf, 0, n, dim, p.ncol, 0, 0u, out, points, sc, stream, -1, nullptr)) return rc;
     if (tree_points && !p.ncol) {
         k_gather_rows<<<148 * 8, 256, 0, stream>>>(points, perm, N, dim, tree_points);
         KD_LAUNCH_CHECK("k_gather_rows");

@@ -82,3 +82,16 @@ extern "C" int kd_build_gpu_noalloc(const float* points, int64_t n, int dim, int
     // same kernels, same order, same results as kd_build_gpu; it zeroes the histogram and error words itself
     return kd::build_gpu(points, n, dim, perm, tree_points, scratch, kNoAllocScratchBytes, (cudaStream_t)stream);
 }
+
+// Companion of kd_build_status for the built-in scratch: the caller of kd_build_gpu_noalloc never sees a
+// workspace pointer, so it could not ask whether the device-side select of its last build failed.  Copies one
+// int from the scratch array to the host (no allocation) and synchronises the stream.
+extern "C" int kd_build_status_noalloc(int64_t n, int dim, void* stream) {
+    if (n <= 0 || dim <= 0) return kd::fail("kd_build_status_noalloc: bad arguments");
+    const size_t need = kd_build_workspace_bytes(n, dim);
+    if (need == 0 || need > kNoAllocScratchBytes)
+        return kd::fail("kd_build_status_noalloc: no build of this size can have used the built-in scratch");
+    void* scratch = nullptr;
+    if (int rc = scratch_for_current_device(&scratch)) return rc;
+    return kd_build_status(scratch, n, dim, stream);
+}

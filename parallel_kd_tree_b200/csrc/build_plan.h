@@ -77,8 +77,10 @@ __device__ __forceinline__ void seg_range(unsigned N, int level, unsigned s, uns
     n = cnt;
 }
 
+// stop_level >= 0: only the select/partition levels [0, stop_level) run (stop_level must lie above the level of
+// the shared-memory builder, i.e. (n >> stop_level) > kFinishT) and *cur_out receives the buffer holding the result.
 int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, unsigned out_lo, OutPtrs out,
-               const float* points, BuildScratch sc, cudaStream_t stream);
+               const float* points, BuildScratch sc, cudaStream_t stream, int stop_level, int* cur_out);
 void count_launch();
 void reset_launches();
 #endif

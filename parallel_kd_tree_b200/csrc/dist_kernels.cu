@@ -27,6 +27,7 @@
 #include <algorithm>
 #include <cstdint>
 #include <cstring>
+#include <mutex>
 #include <string>
 
 #include "../../include/kdtree_b200.h"
@@ -156,18 +157,31 @@ __device__ __forceinline__ Cols cols_of(const DistParams& P, int r, int b) {
 }
 
 // ------------------------------------------------------------------------------------------------
-__global__ void k_dist_init(DistParams P, const float* __restrict__ pts, unsigned local_n, unsigned first_row) {
-    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+// AoS rows -> SoA columns of the rank's slice through a shared-memory tile (rows read as one flat coalesced run,
+// every column written as a coalesced run; same scheme as k_init of the single-GPU build)
+constexpr int kDInitRows = 1024, kDInitBlock = 256;
+__global__ void __launch_bounds__(kDInitBlock) k_dist_init(DistParams P, const float* __restrict__ pts, unsigned local_n,
+                                                          unsigned first_row) {
+    __shared__ float tile[kDInitRows * kMaxCarry];
+    const unsigned row0 = blockIdx.x * kDInitRows, tid = threadIdx.x;
     Cols dst = cols_of(P, P.rank, 0);
-    if (i == 0) {
+    if (blockIdx.x == 0 && tid == 0) {
         DistCtl* c = DCTL(P, P.rank);
         c->cnt = local_n;
         c->err = 0;
         c->ticket = 0;
     }
-    if (i >= local_n) return;
-    dst.idx[i] = (int32_t)(first_row + i);
-    for (int c = 0; c < P.ncol; ++c) dst.c[c][i] = pts[(size_t)i * P.dim + c];
+    if (row0 >= local_n) return;
+    const unsigned rows = min((unsigned)kDInitRows, local_n - row0);
+    for (unsigned r = tid; r < rows; r += kDInitBlock) dst.idx[row0 + r] = (int32_t)(first_row + row0 + r);
+    const unsigned total = rows * (unsigned)P.dim;
+    const float* __restrict__ src = pts + (size_t)row0 * P.dim;
+#pragma unroll 4
+    for (unsigned e = tid; e < total; e += kDInitBlock) tile[e] = src[e];
+    __syncthreads();
+    for (int c = 0; c < P.ncol; ++c)
+#pragma unroll 4
+        for (unsigned r = tid; r < rows; r += kDInitBlock) dst.c[c][row0 + r] = tile[r * P.dim + c];
 }
 
 __global__ void k_dist_state_init(DistParams P, LevelGeo g) {
@@ -743,6 +757,61 @@ static int dist_levels(int world) {
     return l;
 }
 
+// K7, bulk part: a finished slice of this rank's tree arrays -> every other GPU's tree arrays.  With an NVLS
+// multicast mapping ONE 16-byte store per chunk is fanned out by the switch (multimem.st lowers to a plain STG on
+// the multicast address); otherwise one store per peer.  Runs on a side stream while the next slice is built.
+struct RepDst { int32_t* perm[kMaxWorld]; float* tp[kMaxWorld]; int n; };
+
+__device__ __forceinline__ void rep_copy(const unsigned* __restrict__ src, unsigned* const* dst, int nd, size_t words,
+                                         size_t tid, size_t nth) {
+    // words [0, words) of src -> the same offsets of every dst; src and dst share their alignment phase
+    const size_t head = min(words, (size_t)((4u - ((reinterpret_cast<uintptr_t>(src) >> 2) & 3u)) & 3u));
+    const size_t body = (words - head) >> 2;
+    for (size_t i = tid; i < head; i += nth)
+        for (int d = 0; d < nd; ++d) dst[d][i] = src[i];
+    const uint4* __restrict__ s4 = reinterpret_cast<const uint4*>(src + head);
+    for (size_t i = tid; i < body; i += nth) {
+        const uint4 v = __ldcs(&s4[i]);
+        for (int d = 0; d < nd; ++d) reinterpret_cast<uint4*>(dst[d] + head)[i] = v;
+    }
+    for (size_t i = head + (body << 2) + tid; i < words; i += nth)
+        for (int d = 0; d < nd; ++d) dst[d][i] = src[i];
+}
+
+__global__ void __launch_bounds__(512) k_replicate(const int32_t* __restrict__ perm, const float* __restrict__ tp,
+                                                   RepDst dst, size_t first, size_t count, int dim) {
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
+    unsigned* d[kMaxWorld];
+    for (int r = 0; r < dst.n; ++r) d[r] = reinterpret_cast<unsigned*>(dst.perm[r] + first);
+    rep_copy(reinterpret_cast<const unsigned*>(perm + first), d, dst.n, count, tid, nth);
+    if (tp) {
+        for (int r = 0; r < dst.n; ++r) d[r] = reinterpret_cast<unsigned*>(dst.tp[r] + first * dim);
+        rep_copy(reinterpret_cast<const unsigned*>(tp + first * dim), d, dst.n, count * dim, tid, nth);
+    }
+}
+
+// side stream + events of the overlapped replication, one set per device
+struct SideStream { cudaStream_t s; cudaEvent_t ev[8]; bool ok; };
+static int side_stream(SideStream** out) {
+    static std::mutex mu;
+    static SideStream tab[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return fail("kd_dist: cudaGetDevice failed");
+    std::lock_guard<std::mutex> lock(mu);
+    SideStream& S = tab[dev];
+    if (!S.ok) {
+        if (cudaStreamCreateWithFlags(&S.s, cudaStreamNonBlocking) != cudaSuccess) return fail("kd_dist: cudaStreamCreate failed");
+        for (auto& e : S.ev)
+            if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return fail("kd_dist: cudaEventCreate failed");
+        S.ok = true;
+    }
+    *out = &S;
+    return 0;
+}
+
+constexpr int kChunkLevel = 2;                 // the local phase is finished in 1 << kChunkLevel slices ...
+constexpr unsigned kChunkMinLocal = 1u << 21;  // ... when a GPU holds at least this many points
+
 static int local_build(const HostCtx& H, cudaStream_t st) {
     const DistParams& P = H.P;
     const int L = dist_levels(P.world);
@@ -767,18 +836,56 @@ static int local_build(const HostCtx& H, cudaStream_t st) {
         cudaMemsetAsync(sc.err, 0, 256, st) != cudaSuccess)
         return fail("kd_dist_local_build: cudaMemsetAsync failed");
     OutPtrs out{};
+    RepDst rep{};
     if (P.mc) {  // one replica: the multicast mapping, the switch fans the stores out to every GPU
         out.n = 1;
         out.perm[0] = (int32_t*)(P.mc + P.L.perm);
         out.tp[0] = H.with_tp ? (float*)(P.mc + P.L.tp) : nullptr;
+        rep.n = 1;
+        rep.perm[0] = out.perm[0];
+        rep.tp[0] = out.tp[0];
     } else {
         out.n = P.world;
         for (int r = 0; r < P.world; ++r) {
             out.perm[r] = (int32_t*)(P.heap[r] + P.L.perm);
             out.tp[r] = H.with_tp ? (float*)(P.heap[r] + P.L.tp) : nullptr;
+            if (r != P.rank) { rep.perm[rep.n] = out.perm[r]; rep.tp[rep.n] = out.tp[r]; ++rep.n; }
         }
     }
-    return build_core(buf, L & 1, (int64_t)n, P.dim, P.ncol, L, lo, out, nullptr, sc, st);
+    if (P.world == 1 || n < kChunkMinLocal)
+        return build_core(buf, L & 1, (int64_t)n, P.dim, P.ncol, L, lo, out, nullptr, sc, st, -1, nullptr);
+
+    // Overlap of the sub-tree all-gather with the local phase: the top kChunkLevel local levels run on the whole
+    // slice (their few nodes go to every replica directly); then the slice is finished range by range into this
+    // GPU's OWN tree arrays, and every finished range is pushed to the peers on a side stream while the next range
+    // is being built.  3.3 GB arrive at every GPU in an 8-GPU build of 2^28 x 3: >= 4.3 ms of link time that used
+    // to follow the local phase now run next to it.
+    SideStream* S = nullptr;
+    if (int rc = side_stream(&S)) return rc;
+    int cur = L & 1;
+    if (int rc = build_core(buf, cur, (int64_t)n, P.dim, P.ncol, L, lo, out, nullptr, sc, st, kChunkLevel, &cur)) return rc;
+    OutPtrs own{};
+    own.n = 1;
+    own.perm[0] = (int32_t*)(base + P.L.perm);
+    own.tp[0] = H.with_tp ? (float*)(base + P.L.tp) : nullptr;
+    for (unsigned c = 0; c < (1u << kChunkLevel); ++c) {
+        unsigned clo, cn;
+        host_seg_range(n, kChunkLevel, c, clo, cn);
+        Cols sb[2];
+        for (int b = 0; b < 2; ++b) {
+            for (int k = 0; k < kMaxCarry; ++k) sb[b].c[k] = buf[b].c[k] ? buf[b].c[k] + clo : nullptr;
+            sb[b].idx = buf[b].idx + clo;
+        }
+        if (int rc = build_core(sb, cur, (int64_t)cn, P.dim, P.ncol, L + kChunkLevel, lo + clo, own, nullptr, sc, st, -1, nullptr))
+            return rc;
+        if (cudaEventRecord(S->ev[c], st) != cudaSuccess || cudaStreamWaitEvent(S->s, S->ev[c], 0) != cudaSuccess)
+            return fail("kd_dist_local_build: event hand-over to the replication stream failed");
+        k_replicate<<<96, 512, 0, S->s>>>(own.perm[0], own.tp[0], rep, (size_t)lo + clo, (size_t)cn, P.dim);
+        KD_DLAUNCH("k_replicate");
+    }
+    if (cudaEventRecord(S->ev[7], S->s) != cudaSuccess || cudaStreamWaitEvent(st, S->ev[7], 0) != cudaSuccess)
+        return fail("kd_dist_local_build: joining the replication stream failed");
+    return 0;
 }
 
 }  // namespace kd
@@ -830,8 +937,8 @@ int kd_dist_init(const kd_dist_ctx* ctx, const float* local_points, int64_t loca
     cudaStream_t st = (cudaStream_t)stream;
     // control words and flags start at zero once per heap; epochs only grow afterwards
     kd::reset_launches();
-    kd::k_dist_init<<<(unsigned)((local_n + 255) / 256), 256, 0, st>>>(H.P, local_points, (unsigned)local_n,
-                                                                      (unsigned)first_row);
+    kd::k_dist_init<<<(unsigned)((local_n + kd::kDInitRows - 1) / kd::kDInitRows), kd::kDInitBlock, 0, st>>>(
+        H.P, local_points, (unsigned)local_n, (unsigned)first_row);
     kd::count_launch();
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : kd::fail(std::string("kd_dist_init: ") + cudaGetErrorString(e));

@@ -50,6 +50,21 @@ def test_emulated_ranks_eight_dimensions(kd):
         assert torch.equal(outs[0][1].cpu(), pts[ref.long()])
 
 
+def test_emulated_ranks_chunked_local_phase(kd):
+    # >= 2^21 points per rank: the local phase is finished range by range and replicated from a side stream
+    from parallel_kd_tree_b200.parallel.dist_build import EmulatedDistBuild
+    for n, dim, world in [((1 << 23) + 3, 3, 2), (1 << 23, 2, 4)]:
+        pts = kd.ops.generate_uniform(7, dim, n)
+        ref = kd.ops.build(pts.cuda())[0]
+        eb = EmulatedDistBuild(n, dim, world)
+        for trial in range(2):
+            outs = eb.build(pts)
+            torch.cuda.synchronize()
+            for r, (perm, tp) in enumerate(outs):
+                assert torch.equal(perm, ref), f"n={n} world={world} rank {r} trial {trial}"
+            assert torch.equal(outs[-1][1].cpu(), pts[ref.cpu().long()])
+
+
 def test_library_sort_baseline_on_gpu_matches(kd):
     from parallel_kd_tree_b200.parallel.nccl_baseline import sort_build
     pts = kd.ops.generate_uniform(2, 3, 200000)

@@ -35,6 +35,9 @@ def _noalloc(lib, pts):
     rc = lib.kd_build_gpu_noalloc(pts.data_ptr(), n, dim, perm.data_ptr(), tp.data_ptr(),
                                   torch.cuda.current_stream().cuda_stream)
     assert rc == 0, lib.kd_last_error()
+    # the device-side error word lives in the built-in scratch; this is the only way for such a caller to read it
+    rc = lib.kd_build_status_noalloc(n, dim, torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, lib.kd_last_error()
     return perm, tp
 
 
