@@ -26,6 +26,7 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -809,8 +810,14 @@ static int side_stream(SideStream** out) {
     return 0;
 }
 
-constexpr int kChunkLevel = 2;                 // the local phase is finished in 1 << kChunkLevel slices ...
-constexpr unsigned kChunkMinLocal = 1u << 21;  // ... when a GPU holds at least this many points
+constexpr unsigned kChunkMinLocal = 1u << 21;  // the local phase is finished in slices when a GPU holds at least this many points
+// 1 << chunk_level() slices (KD_DIST_CHUNK_LEVEL).  Default 0 = off: measured on 8 B200 at 2^28 x 3 the sliced local
+// phase LOSES (19.3 ms unsliced, 21.5 ms with 2 slices, 23.1 ms with 4): every slice repeats the latency-bound top
+// levels (~17 dependent launches per level), which costs more than the hidden link time (profiles/ROOFLINE.md).
+static int chunk_level() {
+    static const int v = [] { const char* e = std::getenv("KD_DIST_CHUNK_LEVEL"); int x = e ? std::atoi(e) : 0; return x < 0 ? 0 : (x > 3 ? 3 : x); }();
+    return v;
+}
 
 static int local_build(const HostCtx& H, cudaStream_t st) {
     const DistParams& P = H.P;
@@ -852,7 +859,8 @@ static int local_build(const HostCtx& H, cudaStream_t st) {
             if (r != P.rank) { rep.perm[rep.n] = out.perm[r]; rep.tp[rep.n] = out.tp[r]; ++rep.n; }
         }
     }
-    if (P.world == 1 || n < kChunkMinLocal)
+    const int kChunkLevel = chunk_level();
+    if (P.world == 1 || n < kChunkMinLocal || kChunkLevel == 0)
         return build_core(buf, L & 1, (int64_t)n, P.dim, P.ncol, L, lo, out, nullptr, sc, st, -1, nullptr);
 
     // Overlap of the sub-tree all-gather with the local phase: the top kChunkLevel local levels run on the whole

@@ -50,8 +50,31 @@ def test_emulated_ranks_eight_dimensions(kd):
         assert torch.equal(outs[0][1].cpu(), pts[ref.long()])
 
 
-def test_emulated_ranks_chunked_local_phase(kd):
-    # >= 2^21 points per rank: the local phase is finished range by range and replicated from a side stream
+def test_emulated_ranks_chunked_local_phase(kd, monkeypatch):
+    # >= 2^21 points per rank with KD_DIST_CHUNK_LEVEL set (read once per process, so set it before the first
+    # distributed build of this process: the test is a no-op for the sliced path otherwise, see the subprocess below)
+    import os
+    import subprocess
+    import sys
+    code = ("import torch, parallel_kd_tree_b200 as kd\n"
+            "from parallel_kd_tree_b200.parallel.dist_build import EmulatedDistBuild\n"
+            "for n, dim, world in [((1 << 23) + 3, 3, 2), (1 << 23, 2, 4)]:\n"
+            "    pts = kd.ops.generate_uniform(7, dim, n)\n"
+            "    ref = kd.ops.build(pts.cuda())[0]\n"
+            "    eb = EmulatedDistBuild(n, dim, world)\n"
+            "    for trial in range(2):\n"
+            "        outs = eb.build(pts)\n"
+            "        torch.cuda.synchronize()\n"
+            "        assert all(torch.equal(p, ref) for p, _ in outs)\n"
+            "    assert torch.equal(outs[-1][1].cpu(), pts[ref.cpu().long()])\n"
+            "print('sliced ok')\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, env=dict(os.environ, KD_DIST_CHUNK_LEVEL="2"),
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "sliced ok" in r.stdout, r.stdout + r.stderr
+
+
+def test_emulated_ranks_large_local_phase(kd):
     from parallel_kd_tree_b200.parallel.dist_build import EmulatedDistBuild
     for n, dim, world in [((1 << 23) + 3, 3, 2), (1 << 23, 2, 4)]:
         pts = kd.ops.generate_uniform(7, dim, n)
