@@ -94,6 +94,14 @@ int64_t kd_last_launch_count(void);
 int kd_nearest_gpu(const float* tree_points, const int32_t* perm, int64_t n, int dim, const float* queries,
                    int64_t nq, int32_t* out_index, float* out_dist2, float* out_dist, int32_t* out_visited,
                    void* stream);
+/* The same answers for high-dimensional trees, where the reference's pruning never fires and every query visits all
+ * n nodes (its default 500000 x 128 problem, Utility.cpp:98-99): node-parallel exact distances (every sum in the
+ * reference's order, kdtree_sequential.cpp:14-25), a per-query proof that nothing is pruned, the thread-per-query
+ * traversal for the queries where the proof fails.  workspace: kd_nearest_dense_workspace_bytes(n, nq) bytes. */
+size_t kd_nearest_dense_workspace_bytes(int64_t n, int64_t nq);
+int kd_nearest_dense_gpu(const float* tree_points, const int32_t* perm, int64_t n, int dim, const float* queries,
+                         int64_t nq, int32_t* out_index, float* out_dist2, float* out_dist, int32_t* out_visited,
+                         void* workspace, size_t workspace_bytes, void* stream);
 /* Batched k-NN (extension; the reference has k = 1): the reference traversal with a bounded sorted list of the k
  * best nodes; outputs [nq][k] ascending, -1 / +inf padded; 1 <= k <= 32; k = 1 equals kd_nearest_*. */
 int kd_knn_cpu(const float* points, int64_t n, int dim, const int32_t* perm, const float* queries, int64_t nq, int k,

@@ -13,6 +13,7 @@
 // node(lo, n) = slot lo + n/2, left = (lo, n/2), right = (lo + n/2 + 1, n - n/2 - 1).
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdint>
 #include <string>
 
@@ -37,9 +38,11 @@ constexpr int kMaxDepth = 33;
 __global__ void __launch_bounds__(128) k_nearest(const float* __restrict__ tp, const int32_t* __restrict__ perm,
                                                  unsigned N, int dim, const float* __restrict__ queries, long long nq,
                                                  int32_t* __restrict__ out_index, float* __restrict__ out_d2,
-                                                 float* __restrict__ out_d, int32_t* __restrict__ out_visited) {
+                                                 float* __restrict__ out_d, int32_t* __restrict__ out_visited,
+                                                 const int* __restrict__ need) {
     long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= nq) return;
+    if (need && !need[q]) return;   // already answered by the dense path
     const float* qp = queries + (size_t)q * dim;
     unsigned st_lo[kMaxDepth], st_n[kMaxDepth];
     float st_da2[kMaxDepth];
@@ -135,6 +138,211 @@ __global__ void k_bbox_finish(unsigned* mn, unsigned* mx, int dim) {
     reinterpret_cast<float*>(mx)[d] = back(mx[d]);
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// K10/K11, high-dimensional path.  In high dimension the reference's pruning test da*da < best
+// (kdtree_sequential.cpp:118) never fails: one squared coordinate difference is far below any sum of `dim`
+// of them, so every query walks all N nodes (500 000 of 500 000 at dim 128) and a thread per
+// query would compute N dim-long sums one after the other.  The traversal ORDER, however, only matters for
+// (a) which subtrees are pruned and (b) which of several equally distant nodes is met first.  So:
+//   k_nn_dense    node-parallel: one thread per node runs the full sequential dim-term sum (the reference's
+//                 rounding, kdtree_sequential.cpp:14-25) for up to 16 queries at once, tiles of 256 nodes x 32
+//                 coordinates staged in shared memory; per query the smallest distance and the largest da*da
+//                 over ALL nodes meet in two global atomics per CTA;
+//   k_nn_collect  the nodes that attain the smallest distance (normally one);
+//   k_nn_resolve  if max da*da < min distance, then best >= min distance > da*da at every test the reference
+//                 would make: nothing is pruned, all N nodes are visited, and the answer is the node attaining
+//                 the minimum that the near-first DFS meets first (strict <, kdtree_sequential.cpp:91); ties are
+//                 ordered by walking down from the root to where two candidates part.  Otherwise the query is
+//                 handed to the DFS kernel (k_nearest), which is exact in every case.
+// ------------------------------------------------------------------------------------------------
+constexpr int kDenseQB = 16, kDenseRows = 256, kDenseChunk = 32, kDenseMaxCand = 64;
+
+struct DenseWs {
+    float* dall;          // [kDenseQB][N] distances of the current batch
+    unsigned* gmin;       // [kDenseQB] smallest distance (float bits; distances are >= 0)
+    unsigned* gmaxda;     // [kDenseQB] largest da*da
+    unsigned* ccnt;       // [kDenseQB] nodes attaining the minimum
+    unsigned* cand;       // [kDenseQB][kDenseMaxCand]
+    int* need;            // [nq] 1 = the DFS kernel has to answer this query
+};
+
+__device__ __forceinline__ int slot_depth(unsigned N, unsigned slot) {
+    unsigned lo = 0, n = N;
+    for (int d = 0;; ++d) {
+        const unsigned m = n >> 1, s = lo + m;
+        if (slot == s) return d;
+        if (slot < s) n = m; else { lo = s + 1; n = n - m - 1; }
+    }
+}
+
+__global__ void k_nn_init(DenseWs W) {
+    const int t = threadIdx.x;
+    if (t < kDenseQB) { W.gmin[t] = 0xffffffffu; W.gmaxda[t] = 0u; W.ccnt[t] = 0u; }
+}
+
+__global__ void __launch_bounds__(kDenseRows) k_nn_dense(const float* __restrict__ tp, unsigned N, int dim,
+                                                         const float* __restrict__ queries, int nqb, DenseWs W) {
+    __shared__ float tile[kDenseRows][kDenseChunk + 1];
+    __shared__ float qs[kDenseQB][kDenseChunk];
+    __shared__ unsigned wmin[kDenseRows / 32][kDenseQB], wmax[kDenseRows / 32][kDenseQB];
+    const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const unsigned s0 = blockIdx.x * kDenseRows, slot = s0 + tid;
+    const unsigned rows = min((unsigned)kDenseRows, N - s0);
+    float acc[kDenseQB];
+#pragma unroll
+    for (int q = 0; q < kDenseQB; ++q) acc[q] = 0.f;
+    for (int c0 = 0; c0 < dim; c0 += kDenseChunk) {
+        const int cw = min(kDenseChunk, dim - c0);
+        __syncthreads();
+        for (unsigned r = warp; r < rows; r += kDenseRows / 32)   // one 128-byte run of a row per warp
+            if ((int)lane < cw) tile[r][lane] = tp[(size_t)(s0 + r) * dim + c0 + lane];
+        for (unsigned e = tid; e < (unsigned)(kDenseQB * kDenseChunk); e += kDenseRows) {
+            const int q = e / kDenseChunk, d = e % kDenseChunk;
+            qs[q][d] = (q < nqb && d < cw) ? queries[(size_t)q * dim + c0 + d] : 0.f;
+        }
+        __syncthreads();
+        if (tid < rows) {
+            for (int d = 0; d < cw; ++d) {     // coordinates in order: the sum is the reference's, term by term
+                const float x = tile[tid][d];
+#pragma unroll
+                for (int q = 0; q < kDenseQB; ++q) {
+                    const float t = __fsub_rn(x, qs[q][d]);
+                    acc[q] = __fadd_rn(acc[q], __fmul_rn(t, t));
+                }
+            }
+        }
+    }
+    unsigned da2[kDenseQB];
+    if (tid < rows) {
+        const int axis = slot_depth(N, slot) % dim;
+        const float xa = tp[(size_t)slot * dim + axis];
+#pragma unroll
+        for (int q = 0; q < kDenseQB; ++q) {
+            float v = 0.f;
+            if (q < nqb) {
+                const float da = __fsub_rn(queries[(size_t)q * dim + axis], xa);
+                v = __fmul_rn(da, da);
+                W.dall[(size_t)q * N + slot] = acc[q];
+            }
+            da2[q] = __float_as_uint(v);
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < kDenseQB; ++q) {
+        const bool on = tid < rows && q < nqb;
+        const unsigned mn = __reduce_min_sync(0xffffffffu, on ? __float_as_uint(acc[q]) : 0xffffffffu);
+        const unsigned mx = __reduce_max_sync(0xffffffffu, on ? da2[q] : 0u);
+        if (lane == 0) { wmin[warp][q] = mn; wmax[warp][q] = mx; }
+    }
+    __syncthreads();
+    if (tid < (unsigned)nqb) {
+        unsigned mn = 0xffffffffu, mx = 0u;
+        for (int w = 0; w < kDenseRows / 32; ++w) { mn = min(mn, wmin[w][tid]); mx = max(mx, wmax[w][tid]); }
+        atomicMin(&W.gmin[tid], mn);
+        atomicMax(&W.gmaxda[tid], mx);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_nn_collect(unsigned N, int nqb, DenseWs W) {
+    const unsigned slot = blockIdx.x * 256u + threadIdx.x;
+    if (slot >= N) return;
+    for (int q = 0; q < nqb; ++q)
+        if (__float_as_uint(W.dall[(size_t)q * N + slot]) == W.gmin[q]) {
+            const unsigned p = atomicAdd(&W.ccnt[q], 1u);
+            if (p < (unsigned)kDenseMaxCand) W.cand[q * kDenseMaxCand + p] = slot;
+        }
+}
+
+// true if the near-first DFS of query qp meets slot a before slot b (a != b)
+__device__ bool dfs_before(const float* __restrict__ tp, unsigned N, int dim, const float* __restrict__ qp, unsigned a,
+                           unsigned b) {
+    unsigned lo = 0, n = N;
+    for (int depth = 0;; ++depth) {
+        const unsigned m = n >> 1, s = lo + m;
+        if (a == s) return true;
+        if (b == s) return false;
+        const bool al = a < s, bl = b < s;
+        if (al != bl) {
+            const int axis = depth % dim;
+            const float da = __fsub_rn(qp[axis], tp[(size_t)s * dim + axis]);
+            return al == (da < 0.f);   // the near side (left iff da < 0) is walked first
+        }
+        if (al) n = m; else { lo = s + 1; n = n - m - 1; }
+    }
+}
+
+__global__ void k_nn_resolve(const float* __restrict__ tp, const int32_t* __restrict__ perm, unsigned N, int dim,
+                             const float* __restrict__ queries, int nqb, DenseWs W, int* __restrict__ need,
+                             int32_t* __restrict__ out_index, float* __restrict__ out_d2, float* __restrict__ out_d,
+                             int32_t* __restrict__ out_visited) {
+    const int q = threadIdx.x;
+    if (q >= nqb) return;
+    const float dmin = __uint_as_float(W.gmin[q]), damax = __uint_as_float(W.gmaxda[q]);
+    const unsigned c = W.ccnt[q];
+    if (!(damax < dmin) || c == 0u || c > (unsigned)kDenseMaxCand) { need[q] = 1; return; }
+    const float* qp = queries + (size_t)q * dim;
+    unsigned best = W.cand[q * kDenseMaxCand];
+    for (unsigned k = 1; k < c; ++k) {
+        const unsigned s = W.cand[q * kDenseMaxCand + k];
+        if (dfs_before(tp, N, dim, qp, s, best)) best = s;
+    }
+    need[q] = 0;
+    if (out_index) out_index[q] = perm[best];
+    if (out_d2) out_d2[q] = dmin;
+    if (out_d) out_d[q] = __fsqrt_rn(dmin);
+    if (out_visited) out_visited[q] = (int32_t)N;
+}
+
+}  // namespace kd
+
+extern "C" {
+
+size_t kd_nearest_dense_workspace_bytes(int64_t n, int64_t nq) {
+    if (n <= 0 || nq < 0) return 0;
+    return (size_t)kd::kDenseQB * (size_t)n * 4 + (size_t)kd::kDenseQB * (3 + kd::kDenseMaxCand) * 4 + (size_t)nq * 4 + 1024;
+}
+
+/* 1-NN with the reference's answers (kdtree_sequential.cpp:75-136) for workloads where pruning does not fire
+ * (high dimension): node-parallel exact distances, a proof per query that the reference visits every node, and the
+ * thread-per-query DFS for whatever cannot be proven.  Same outputs as kd_nearest_gpu. */
+int kd_nearest_dense_gpu(const float* tree_points, const int32_t* perm, int64_t n, int dim, const float* queries,
+                         int64_t nq, int32_t* out_index, float* out_dist2, float* out_dist, int32_t* out_visited,
+                         void* workspace, size_t workspace_bytes, void* stream) {
+    if (!tree_points || !perm || !queries || !workspace || n <= 0 || dim <= 0 || nq < 0 || n >= (1ll << 31))
+        return kd::fail("kd_nearest_dense_gpu: bad arguments");
+    if (workspace_bytes < kd_nearest_dense_workspace_bytes(n, nq)) return kd::fail("kd_nearest_dense_gpu: workspace too small");
+    if (nq == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned char* ws = (unsigned char*)workspace;
+    kd::DenseWs W;
+    W.dall = (float*)ws;
+    ws += (size_t)kd::kDenseQB * (size_t)n * 4;
+    W.gmin = (unsigned*)ws;
+    W.gmaxda = W.gmin + kd::kDenseQB;
+    W.ccnt = W.gmaxda + kd::kDenseQB;
+    W.cand = W.ccnt + kd::kDenseQB;
+    W.need = (int*)(W.cand + kd::kDenseQB * kd::kDenseMaxCand);
+    const unsigned N = (unsigned)n;
+    for (int64_t q0 = 0; q0 < nq; q0 += kd::kDenseQB) {
+        const int nqb = (int)std::min<int64_t>(kd::kDenseQB, nq - q0);
+        const float* qb = queries + (size_t)q0 * dim;
+        kd::k_nn_init<<<1, 32, 0, st>>>(W);
+        kd::k_nn_dense<<<(N + kd::kDenseRows - 1) / kd::kDenseRows, kd::kDenseRows, 0, st>>>(tree_points, N, dim, qb, nqb, W);
+        kd::k_nn_collect<<<(N + 255) / 256, 256, 0, st>>>(N, nqb, W);
+        kd::k_nn_resolve<<<1, 32, 0, st>>>(tree_points, perm, N, dim, qb, nqb, W, W.need + q0,
+                                           out_index ? out_index + q0 : nullptr, out_dist2 ? out_dist2 + q0 : nullptr,
+                                           out_dist ? out_dist + q0 : nullptr, out_visited ? out_visited + q0 : nullptr);
+    }
+    kd::k_nearest<<<(unsigned)((nq + 127) / 128), 128, 0, st>>>(tree_points, perm, N, dim, queries, nq, out_index,
+                                                              out_dist2, out_dist, out_visited, W.need);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : kd::fail(std::string("kd_nearest_dense_gpu: ") + cudaGetErrorString(e));
+}
+
+}  // extern "C"
+
+namespace kd {
 }  // namespace kd
 
 extern "C" {
@@ -151,7 +359,7 @@ int kd_nearest_gpu(const float* tree_points, const int32_t* perm, int64_t n, int
         return kd::fail("kd_nearest_gpu: bad arguments");
     if (nq == 0) return 0;
     kd::k_nearest<<<(unsigned)((nq + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
-        tree_points, perm, (unsigned)n, dim, queries, nq, out_index, out_dist2, out_dist, out_visited);
+        tree_points, perm, (unsigned)n, dim, queries, nq, out_index, out_dist2, out_dist, out_visited, nullptr);
     KD_RET_LAUNCH("kd_nearest_gpu");
 }
 

@@ -63,13 +63,13 @@ class KDTree:
         return self.n // 2
 
     # -- queries ---------------------------------------------------------------------------
-    def nearest(self, queries: torch.Tensor) -> NNResult:
-        """Reference 1-NN (kdtree_sequential.cpp:75-136) for a batch of queries."""
+    def nearest(self, queries: torch.Tensor, mode: str = "auto") -> NNResult:
+        """Reference 1-NN (kdtree_sequential.cpp:75-136) for a batch of queries (``mode``: see ``ops.nearest``)."""
         queries = queries.to(self.device, torch.float32)
         if queries.dim() == 1:
             queries = queries[None]
         with trace.span(f"nearest nq={queries.shape[0]}", self.device):
-            idx, d2, d, vis = ops.nearest(self.tree_points, self.perm, queries)
+            idx, d2, d, vis = ops.nearest(self.tree_points, self.perm, queries, mode)
         return NNResult(index=idx, ids=idx + (1 + self.id_offset), dist2=d2, dist=d, visited=vis)
 
     def knn(self, queries: torch.Tensor, k: int):

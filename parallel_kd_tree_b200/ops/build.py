@@ -6,7 +6,7 @@ import ctypes as C
 import torch
 
 from .._lib import KdError, check, lib
-from ._util import as_points, ptr, stream_ptr
+from ._util import as_points, check_out, ptr, stream_ptr
 
 
 def build_workspace_bytes(n: int, dim: int) -> int:
@@ -23,6 +23,8 @@ def build_into(points: torch.Tensor, perm: torch.Tensor, tree_points: torch.Tens
     """Builds into caller-provided outputs (no allocation when ``workspace`` is given)."""
     points = as_points(points)
     n, dim = points.shape
+    check_out(perm, (n,), torch.int32, points.device, "perm")
+    check_out(tree_points, (n, dim), torch.float32, points.device, "tree_points")
     if points.is_cuda:
         need = build_workspace_bytes(n, dim)
         if workspace is None:

@@ -4,29 +4,46 @@ from __future__ import annotations
 import torch
 
 from .._lib import check, lib
-from ._util import as_points, stream_ptr
+import os
+
+from ._util import as_points, on_device, stream_ptr
 
 
-def _nearest_op_impl(tree_points: torch.Tensor, perm: torch.Tensor,
-                queries: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
+# From this dimension on the GPU path first tries the node-parallel kernels (the reference's pruning does not fire
+# in high dimension, so a thread per query would walk all n nodes one after the other); "dfs" / "dense" force a path.
+DENSE_MIN_DIM = int(os.environ.get("KD_B200_DENSE_MIN_DIM", "16"))
+
+
+def _nearest_op_impl(tree_points: torch.Tensor, perm: torch.Tensor, queries: torch.Tensor,
+                     mode: str = "auto") -> tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
     tree_points = as_points(tree_points, "tree_points")
-    queries = as_points(queries, "queries")
+    dev = tree_points.device
+    queries = on_device(as_points(queries, "queries"), dev, torch.float32, "queries")
     n, dim = tree_points.shape
     if queries.shape[1] != dim:
         # the reference exits with "Dimensions do not match!" (kdtree_sequential.cpp:15-18)
         raise ValueError("Dimensions do not match!")
+    if perm.numel() != n:
+        raise ValueError(f"perm has {perm.numel()} entries for a tree of {n} points")
     nq = queries.shape[0]
-    dev = tree_points.device
-    perm = perm.to(torch.int32).contiguous()
+    perm = on_device(perm, dev, torch.int32, "perm")
     idx = torch.empty(nq, dtype=torch.int32, device=dev)
     d2 = torch.empty(nq, dtype=torch.float32, device=dev)
     d = torch.empty(nq, dtype=torch.float32, device=dev)
     if tree_points.is_cuda:
         vis = torch.empty(nq, dtype=torch.int32, device=dev)
+        dense = mode == "dense" or (mode == "auto" and dim >= DENSE_MIN_DIM)
         with torch.cuda.device(dev):
-            check(lib().kd_nearest_gpu(tree_points.data_ptr(), perm.data_ptr(), n, dim, queries.data_ptr(), nq,
-                                       idx.data_ptr(), d2.data_ptr(), d.data_ptr(), vis.data_ptr(),
-                                       stream_ptr(dev)), "kd::nearest")
+            if dense:
+                nbytes = int(lib().kd_nearest_dense_workspace_bytes(n, nq))
+                ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+                check(lib().kd_nearest_dense_gpu(tree_points.data_ptr(), perm.data_ptr(), n, dim, queries.data_ptr(),
+                                                 nq, idx.data_ptr(), d2.data_ptr(), d.data_ptr(), vis.data_ptr(),
+                                                 ws.data_ptr(), nbytes, stream_ptr(dev)), "kd::nearest")
+            else:
+                check(lib().kd_nearest_gpu(tree_points.data_ptr(), perm.data_ptr(), n, dim, queries.data_ptr(), nq,
+                                           idx.data_ptr(), d2.data_ptr(), d.data_ptr(), vis.data_ptr(),
+                                           stream_ptr(dev)), "kd::nearest")
         vis = vis.long()
     else:
         # the CPU core indexes the original rows through perm; tree_points[s] == points[perm[s]]
@@ -39,7 +56,12 @@ def _nearest_op_impl(tree_points: torch.Tensor, perm: torch.Tensor,
     return idx, d2, d, vis
 
 
-_nearest_op = torch.library.custom_op("kd::nearest", mutates_args=())(_nearest_op_impl)
+def _nearest_op_auto(tree_points: torch.Tensor, perm: torch.Tensor,
+                     queries: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
+    return _nearest_op_impl(tree_points, perm, queries, "auto")
+
+
+_nearest_op = torch.library.custom_op("kd::nearest", mutates_args=())(_nearest_op_auto)
 
 
 @_nearest_op.register_fake
@@ -49,15 +71,24 @@ def _(tree_points, perm, queries):
             queries.new_empty(nq, dtype=torch.int64))
 
 
-def nearest(tree_points: torch.Tensor, perm: torch.Tensor, queries: torch.Tensor):
-    """1-NN of every query with the reference's traversal; returns (point index, dist², dist, nodes visited)."""
-    return _nearest_op_impl(tree_points, perm, queries)
+def nearest(tree_points: torch.Tensor, perm: torch.Tensor, queries: torch.Tensor, mode: str = "auto"):
+    """1-NN of every query with the reference's answers; returns (point index, dist², dist, nodes visited).
+
+    ``mode`` (GPU only): "dfs" = one thread per query walks the reference's traversal; "dense" = node-parallel
+    distances + a per-query proof that the reference prunes nothing, DFS for the rest (bit-identical results);
+    "auto" = dense from ``DENSE_MIN_DIM`` dimensions on."""
+    if mode not in ("auto", "dfs", "dense"):
+        raise ValueError("mode must be auto, dfs or dense")
+    return _nearest_op_impl(tree_points, perm, queries, mode)
 
 
 def gather_rows(points: torch.Tensor, perm: torch.Tensor) -> torch.Tensor:
     points = as_points(points)
     if not points.is_cuda:
-        return points.index_select(0, perm.long())
+        return points.index_select(0, perm.to(points.device).long())
+    perm = on_device(perm, points.device, torch.int32, "perm")
+    if perm.numel() != points.shape[0]:
+        raise ValueError("perm and points disagree in length")
     out = torch.empty_like(points)
     with torch.cuda.device(points.device):
         check(lib().kd_gather_rows_gpu(points.data_ptr(), perm.data_ptr(), points.shape[0], points.shape[1],
@@ -124,13 +155,15 @@ def knn(tree_points: torch.Tensor, perm: torch.Tensor, queries: torch.Tensor, k:
     Same traversal as ``nearest`` with a bounded list of the k best nodes; ``k = 1`` gives the reference's answers.
     """
     tree_points = as_points(tree_points, "tree_points")
-    queries = as_points(queries, "queries")
+    dev = tree_points.device
+    queries = on_device(as_points(queries, "queries"), dev, torch.float32, "queries")
     n, dim = tree_points.shape
     if queries.shape[1] != dim:
         raise ValueError("Dimensions do not match!")
+    if perm.numel() != n:
+        raise ValueError(f"perm has {perm.numel()} entries for a tree of {n} points")
     nq = queries.shape[0]
-    dev = tree_points.device
-    perm = perm.to(torch.int32).contiguous()
+    perm = on_device(perm, dev, torch.int32, "perm")
     idx = torch.empty((nq, k), dtype=torch.int32, device=dev)
     d2 = torch.empty((nq, k), dtype=torch.float32, device=dev)
     if tree_points.is_cuda:

@@ -20,6 +20,44 @@ def test_nearest_bits_equal_cpu(kd, seed, dim, n, nq):
     assert torch.equal(res.visited.cpu(), cpu.visited)
 
 
+@pytest.mark.parametrize("seed,dim,n,nq", [(1, 128, 20000, 37), (2, 16, 30000, 100), (3, 33, 4097, 16), (4, 3, 5000, 50),
+                                           (5, 64, 1, 3), (6, 200, 300, 20)])
+def test_dense_path_equals_dfs_path(kd, seed, dim, n, nq):
+    # node-parallel path (+ its DFS fallback where pruning cannot be excluded, e.g. the 3-D case) == thread-per-query DFS
+    pts, qs = kd.ops.generate_problem(seed, dim, n, nq)
+    tree = kd.KDTree(pts.cuda())
+    a, b = tree.nearest(qs.cuda(), mode="dfs"), tree.nearest(qs.cuda(), mode="dense")
+    cpu = kd.KDTree(pts).nearest(qs)
+    for x in (a, b):
+        assert torch.equal(x.index.cpu(), cpu.index)
+        assert torch.equal(x.dist2.cpu().view(torch.int32), cpu.dist2.view(torch.int32))
+        assert torch.equal(x.dist.cpu().view(torch.int32), cpu.dist.view(torch.int32))
+        assert torch.equal(x.visited.cpu(), cpu.visited)
+
+
+def test_dense_path_orders_equal_distances_like_the_traversal(kd):
+    # duplicated points: several nodes attain the smallest distance; the reference keeps the one its DFS meets first
+    g = torch.Generator().manual_seed(5)
+    base = torch.randn(500, 40, generator=g) * 30
+    pts = base[torch.randint(0, 500, (6000,), generator=g)].contiguous()
+    qs = base[:64] + 0.25
+    cpu = kd.KDTree(pts).nearest(qs)
+    res = kd.KDTree(pts.cuda()).nearest(qs.cuda(), mode="dense")
+    assert torch.equal(res.index.cpu(), cpu.index) and torch.equal(res.visited.cpu(), cpu.visited)
+    assert torch.equal(res.dist2.cpu().view(torch.int32), cpu.dist2.view(torch.int32))
+
+
+def test_ops_reject_or_move_foreign_tensors(kd):
+    pts, qs = kd.ops.generate_problem(1, 3, 1000, 5)
+    tree = kd.KDTree(pts.cuda())
+    res = kd.ops.nearest(tree.tree_points, tree.perm.cpu(), qs)          # CPU perm / queries are moved, not dereferenced
+    assert torch.equal(res[0].cpu(), kd.KDTree(pts).nearest(qs).index)
+    with pytest.raises(ValueError):
+        kd.ops.build_into(pts.cuda(), torch.empty(999, dtype=torch.int32, device="cuda"), None)
+    with pytest.raises(ValueError):
+        kd.ops.build_into(pts.cuda(), torch.empty(1000, dtype=torch.int32), None)     # perm on the wrong device
+
+
 def test_default_problem_golden_lines_on_gpu(kd):
     # the graded problem (PDF p.4): 500000 x 128, seed 1; golden = unmodified ./sequential
     golden = ["707.539", "653.765", "693.995", "715.386", "732.924", "702.161", "739.194", "693.53", "698.66",
