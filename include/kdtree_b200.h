@@ -108,6 +108,17 @@ int kd_knn_cpu(const float* points, int64_t n, int dim, const int32_t* perm, con
                int32_t* out_index, float* out_dist2);
 int kd_knn_gpu(const float* tree_points, const int32_t* perm, int64_t n, int dim, const float* queries, int64_t nq,
                int k, int32_t* out_index, float* out_dist2, void* stream);
+/* Coherent batches: kd_query_order_gpu groups the queries by the sub-tree (top `levels` <= 16 levels) their search
+ * enters first (own counting sort: key + histogram + scan + scatter kernels); the *_ordered entry points hand query
+ * order[t] to thread t, so a warp's threads walk the same nodes.  Outputs are indexed by the original query number and
+ * are identical to the unordered calls.  key_scratch: nq uint32; bins_scratch: (1 << levels) uint32. */
+int kd_query_order_gpu(const float* tree_points, int64_t n, int dim, const float* queries, int64_t nq, int levels,
+                       int32_t* order, void* key_scratch, void* bins_scratch, void* stream);
+int kd_nearest_ordered_gpu(const float* tree_points, const int32_t* perm, int64_t n, int dim, const float* queries,
+                           int64_t nq, const int32_t* order, int32_t* out_index, float* out_dist2, float* out_dist,
+                           int32_t* out_visited, void* stream);
+int kd_knn_ordered_gpu(const float* tree_points, const int32_t* perm, int64_t n, int dim, const float* queries,
+                       int64_t nq, int k, const int32_t* order, int32_t* out_index, float* out_dist2, void* stream);
 int kd_gather_rows_gpu(const float* points, const int32_t* perm, int64_t n, int dim, float* out, void* stream);
 int kd_materialize_nodes_gpu(int64_t n, const int32_t* perm, int32_t* node_point, int32_t* left, int32_t* right,
                              void* stream);

@@ -56,6 +56,9 @@ def _declare(lib):
         "kd_nearest_gpu": (i32, [vp, vp, i64, i32, vp, i64, vp, vp, vp, vp, vp]),
         "kd_nearest_dense_workspace_bytes": (C.c_size_t, [i64, i64]),
         "kd_nearest_dense_gpu": (i32, [vp, vp, i64, i32, vp, i64, vp, vp, vp, vp, vp, C.c_size_t, vp]),
+        "kd_query_order_gpu": (i32, [vp, i64, i32, vp, i64, i32, vp, vp, vp, vp]),
+        "kd_nearest_ordered_gpu": (i32, [vp, vp, i64, i32, vp, i64, vp, vp, vp, vp, vp, vp]),
+        "kd_knn_ordered_gpu": (i32, [vp, vp, i64, i32, vp, i64, i32, vp, vp, vp, vp]),
         "kd_knn_cpu": (i32, [vp, i64, i32, vp, vp, i64, i32, vp, vp]),
         "kd_knn_gpu": (i32, [vp, vp, i64, i32, vp, i64, i32, vp, vp, vp]),
         "kd_gather_rows_gpu": (i32, [vp, vp, i64, i32, vp, vp]),

@@ -34,37 +34,93 @@ __device__ __forceinline__ float dist2_exact(const float* __restrict__ a, const 
 
 constexpr int kMaxDepth = 33;
 
-// one thread per query; explicit stack of postponed far sides
+// Row access for the traversal kernels.  DIM > 0: the query lives in registers, a node row is fetched with the widest
+// aligned vector load and the split-axis coordinate is picked with a select chain (no dynamic register index);
+// DIM == 0: any dimension, coordinates are re-read from memory.
+template <int DIM>
+struct RowOps {
+    float q[DIM];
+    __device__ __forceinline__ void load_query(const float* __restrict__ qp, int) {
+#pragma unroll
+        for (int i = 0; i < DIM; ++i) q[i] = qp[i];
+    }
+    __device__ __forceinline__ void visit(const float* __restrict__ pp, int, int axis, float& de, float& da) const {
+        float p[DIM];
+        if (DIM % 4 == 0) {
+#pragma unroll
+            for (int i = 0; i < DIM; i += 4) {
+                const float4 v = __ldg(reinterpret_cast<const float4*>(pp + i));
+                p[i] = v.x; p[i + 1] = v.y; p[i + 2] = v.z; p[i + 3] = v.w;
+            }
+        } else if (DIM % 2 == 0) {
+#pragma unroll
+            for (int i = 0; i < DIM; i += 2) {
+                const float2 v = __ldg(reinterpret_cast<const float2*>(pp + i));
+                p[i] = v.x; p[i + 1] = v.y;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < DIM; ++i) p[i] = __ldg(pp + i);
+        }
+        float dist = 0.f, pa = p[0], qa = q[0];
+#pragma unroll
+        for (int i = 0; i < DIM; ++i) {
+            const float t = __fsub_rn(p[i], q[i]);
+            dist = __fadd_rn(dist, __fmul_rn(t, t));
+            if (i > 0 && axis == i) { pa = p[i]; qa = q[i]; }
+        }
+        de = dist;
+        da = __fsub_rn(qa, pa);
+    }
+};
+template <>
+struct RowOps<0> {
+    const float* qp_;
+    __device__ __forceinline__ void load_query(const float* __restrict__ qp, int) { qp_ = qp; }
+    __device__ __forceinline__ void visit(const float* __restrict__ pp, int dim, int axis, float& de, float& da) const {
+        de = dist2_exact(pp, qp_, dim);
+        da = __fsub_rn(qp_[axis], pp[axis]);
+    }
+};
+
+// one thread per query; explicit stack of postponed far sides.  `order` (optional) lists the queries so that the
+// threads of a warp hold queries that walk the same part of the tree (k_qkey / k_qscatter below): their loads then
+// hit the same lines and their loops stay in step.  The split axis is carried along (axis + 1 mod dim per level)
+// instead of being recomputed with an integer division per node.
+template <int DIM>
 __global__ void __launch_bounds__(128) k_nearest(const float* __restrict__ tp, const int32_t* __restrict__ perm,
                                                  unsigned N, int dim, const float* __restrict__ queries, long long nq,
                                                  int32_t* __restrict__ out_index, float* __restrict__ out_d2,
                                                  float* __restrict__ out_d, int32_t* __restrict__ out_visited,
-                                                 const int* __restrict__ need) {
-    long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= nq) return;
+                                                 const int* __restrict__ need, const int32_t* __restrict__ order) {
+    long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nq) return;
+    const long long q = order ? (long long)order[t] : t;
     if (need && !need[q]) return;   // already answered by the dense path
-    const float* qp = queries + (size_t)q * dim;
+    if (DIM > 0) dim = DIM;
+    RowOps<DIM> R;
+    R.load_query(queries + (size_t)q * dim, dim);
     unsigned st_lo[kMaxDepth], st_n[kMaxDepth];
     float st_da2[kMaxDepth];
-    unsigned char st_depth[kMaxDepth];
+    unsigned short st_axis[kMaxDepth];
     int sp = 0;
     unsigned best = N >> 1;  // nearest_neighbor(): best starts at the root (kdtree_sequential.cpp:133-136)
-    float best_d = dist2_exact(tp + (size_t)best * dim, qp, dim);
+    float best_d, da_unused;
+    R.visit(tp + (size_t)best * dim, dim, 0, best_d, da_unused);
     unsigned lo = 0, cnt = N;
-    int depth = 0, visited = 0;
+    int axis = 0, visited = 0;
     for (;;) {
         while (cnt > 0) {
             unsigned m = cnt >> 1, slot = lo + m;
-            const float* pp = tp + (size_t)slot * dim;
-            int axis = depth % dim;
-            float de = dist2_exact(pp, qp, dim);
-            float da = __fsub_rn(qp[axis], pp[axis]);
+            float de, da;
+            R.visit(tp + (size_t)slot * dim, dim, axis, de, da);
             ++visited;
             if (de < best_d) { best_d = de; best = slot; }
             unsigned rlo = slot + 1, rn = cnt - m - 1;
             float da2 = __fmul_rn(da, da);
+            axis = axis + 1 == dim ? 0 : axis + 1;
             st_da2[sp] = da2;
-            st_depth[sp] = (unsigned char)(depth + 1);
+            st_axis[sp] = (unsigned short)axis;
             if (da < 0.f) {
                 st_lo[sp] = rlo; st_n[sp] = rn;
                 cnt = m;
@@ -73,13 +129,12 @@ __global__ void __launch_bounds__(128) k_nearest(const float* __restrict__ tp, c
                 lo = rlo; cnt = rn;
             }
             ++sp;
-            ++depth;
         }
         bool resumed = false;
         while (sp > 0) {
             --sp;
             if (st_n[sp] > 0 && st_da2[sp] < best_d) {
-                lo = st_lo[sp]; cnt = st_n[sp]; depth = st_depth[sp];
+                lo = st_lo[sp]; cnt = st_n[sp]; axis = st_axis[sp];
                 resumed = true;
                 break;
             }
@@ -90,6 +145,58 @@ __global__ void __launch_bounds__(128) k_nearest(const float* __restrict__ tp, c
     if (out_d2) out_d2[q] = best_d;
     if (out_d) out_d[q] = __fsqrt_rn(best_d);
     if (out_visited) out_visited[q] = visited;
+}
+
+// ---- query ordering: key = the near-side path through the top `levels` levels of the tree ----
+// (queries with the same key descend into the same sub-tree first; a counting sort on the key groups them)
+__global__ void __launch_bounds__(256) k_qkey(const float* __restrict__ tp, unsigned N, int dim,
+                                              const float* __restrict__ queries, long long nq, int levels,
+                                              unsigned* __restrict__ key, unsigned* __restrict__ hist) {
+    long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    const float* qp = queries + (size_t)q * dim;
+    unsigned lo = 0, cnt = N, k = 0;
+    int axis = 0;
+    for (int l = 0; l < levels; ++l) {
+        k <<= 1;
+        if (cnt > 0) {
+            const unsigned m = cnt >> 1, slot = lo + m;
+            const float da = __fsub_rn(qp[axis], tp[(size_t)slot * dim + axis]);
+            if (da < 0.f) cnt = m; else { k |= 1u; lo = slot + 1; cnt = cnt - m - 1; }
+            axis = axis + 1 == dim ? 0 : axis + 1;
+        }
+    }
+    key[q] = k;
+    atomicAdd(&hist[k], 1u);
+}
+
+// exclusive scan of hist[0 .. bins) in place, one CTA (bins <= 65536)
+__global__ void __launch_bounds__(1024) k_qscan(unsigned* __restrict__ hist, unsigned bins) {
+    __shared__ unsigned wsum[32];
+    __shared__ unsigned carry;
+    const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    if (tid == 0) carry = 0u;
+    __syncthreads();
+    for (unsigned b0 = 0; b0 < bins; b0 += 1024u) {
+        const unsigned i = b0 + tid, v = i < bins ? hist[i] : 0u;
+        unsigned inc = v;
+        for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= (unsigned)o) inc += t; }
+        if (lane == 31) wsum[warp] = inc;
+        __syncthreads();
+        unsigned base = carry;
+        for (unsigned w = 0; w < warp; ++w) base += wsum[w];
+        if (i < bins) hist[i] = base + inc - v;
+        __syncthreads();
+        if (tid == 1023) carry = base + inc;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) k_qscatter(const unsigned* __restrict__ key, unsigned* __restrict__ cursor,
+                                                  long long nq, int32_t* __restrict__ order) {
+    long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    order[atomicAdd(&cursor[key[q]], 1u)] = (int32_t)q;
 }
 
 // K9: Node{point,left,right} arrays indexed by in-order slot (Node.hpp:35-45); -1 = nullptr
@@ -334,8 +441,8 @@ int kd_nearest_dense_gpu(const float* tree_points, const int32_t* perm, int64_t 
                                            out_index ? out_index + q0 : nullptr, out_dist2 ? out_dist2 + q0 : nullptr,
                                            out_dist ? out_dist + q0 : nullptr, out_visited ? out_visited + q0 : nullptr);
     }
-    kd::k_nearest<<<(unsigned)((nq + 127) / 128), 128, 0, st>>>(tree_points, perm, N, dim, queries, nq, out_index,
-                                                              out_dist2, out_dist, out_visited, W.need);
+    kd::k_nearest<0><<<(unsigned)((nq + 127) / 128), 128, 0, st>>>(tree_points, perm, N, dim, queries, nq, out_index,
+                                                                 out_dist2, out_dist, out_visited, W.need, nullptr);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : kd::fail(std::string("kd_nearest_dense_gpu: ") + cudaGetErrorString(e));
 }
@@ -346,6 +453,21 @@ namespace kd {
 }  // namespace kd
 
 extern "C" {
+
+// dim 1..8 run the register-resident specialisations (vector loads need rows aligned to their width: the tree
+// arrays of this library are; foreign pointers fall back to the generic kernel)
+#define KD_DIM_DISPATCH(dim, aligned, CALL)                 \
+    switch ((aligned) ? (dim) : 0) {                        \
+        case 1: { constexpr int D = 1; CALL; } break;       \
+        case 2: { constexpr int D = 2; CALL; } break;       \
+        case 3: { constexpr int D = 3; CALL; } break;       \
+        case 4: { constexpr int D = 4; CALL; } break;       \
+        case 5: { constexpr int D = 5; CALL; } break;       \
+        case 6: { constexpr int D = 6; CALL; } break;       \
+        case 7: { constexpr int D = 7; CALL; } break;       \
+        case 8: { constexpr int D = 8; CALL; } break;       \
+        default: { constexpr int D = 0; CALL; } break;      \
+    }
 
 #define KD_RET_LAUNCH(what)                                                                       \
     do {                                                                                          \
@@ -358,9 +480,39 @@ int kd_nearest_gpu(const float* tree_points, const int32_t* perm, int64_t n, int
     if (!tree_points || !perm || !queries || n <= 0 || dim <= 0 || nq < 0 || n >= (1ll << 31))
         return kd::fail("kd_nearest_gpu: bad arguments");
     if (nq == 0) return 0;
-    kd::k_nearest<<<(unsigned)((nq + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
-        tree_points, perm, (unsigned)n, dim, queries, nq, out_index, out_dist2, out_dist, out_visited, nullptr);
-    KD_RET_LAUNCH("kd_nearest_gpu");
+    return kd_nearest_ordered_gpu(tree_points, perm, n, dim, queries, nq, nullptr, out_index, out_dist2, out_dist,
+                                  out_visited, stream);
+}
+
+/* Ordering of a query batch for coherent traversal: order[t] = index of the t-th query when the queries are grouped
+ * by the sub-tree (of depth `levels` <= 16) their search descends into first.  key: nq uint32 of scratch; bins:
+ * (1 << levels) uint32 of scratch.  Results of the *_ordered entry points do not depend on the order. */
+int kd_query_order_gpu(const float* tree_points, int64_t n, int dim, const float* queries, int64_t nq, int levels,
+                       int32_t* order, void* key_scratch, void* bins_scratch, void* stream) {
+    if (!tree_points || !queries || !order || !key_scratch || !bins_scratch || n <= 0 || dim <= 0 || nq < 0 || levels < 1 ||
+        levels > 16 || n >= (1ll << 31) || nq >= (1ll << 31))
+        return kd::fail("kd_query_order_gpu: bad arguments (1 <= levels <= 16)");
+    if (nq == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned bins = 1u << levels;
+    if (cudaMemsetAsync(bins_scratch, 0, (size_t)bins * 4, st) != cudaSuccess) return kd::fail("kd_query_order_gpu: memset failed");
+    kd::k_qkey<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(tree_points, (unsigned)n, dim, queries, nq, levels,
+                                                           (unsigned*)key_scratch, (unsigned*)bins_scratch);
+    kd::k_qscan<<<1, 1024, 0, st>>>((unsigned*)bins_scratch, bins);
+    kd::k_qscatter<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>((const unsigned*)key_scratch, (unsigned*)bins_scratch, nq, order);
+    KD_RET_LAUNCH("kd_query_order_gpu");
+}
+
+int kd_nearest_ordered_gpu(const float* tree_points, const int32_t* perm, int64_t n, int dim, const float* queries,
+                           int64_t nq, const int32_t* order, int32_t* out_index, float* out_dist2, float* out_dist,
+                           int32_t* out_visited, void* stream) {
+    if (!tree_points || !perm || !queries || n <= 0 || dim <= 0 || nq < 0 || n >= (1ll << 31))
+        return kd::fail("kd_nearest_ordered_gpu: bad arguments");
+    if (nq == 0) return 0;
+    const bool aligned = ((uintptr_t)tree_points & 15u) == 0;
+    KD_DIM_DISPATCH(dim, aligned, (kd::k_nearest<D><<<(unsigned)((nq + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+        tree_points, perm, (unsigned)n, dim, queries, nq, out_index, out_dist2, out_dist, out_visited, nullptr, order)));
+    KD_RET_LAUNCH("kd_nearest_ordered_gpu");
 }
 
 int kd_materialize_nodes_gpu(int64_t n, const int32_t* perm, int32_t* node_point, int32_t* left, int32_t* right,
@@ -401,27 +553,30 @@ int kd_bbox_gpu(const float* points, int64_t n, int dim, float* out_min, float* 
 namespace kd {
 constexpr int kMaxK = 32;
 
+template <int DIM>
 __global__ void __launch_bounds__(128) k_knn(const float* __restrict__ tp, const int32_t* __restrict__ perm, unsigned N,
                                              int dim, const float* __restrict__ queries, long long nq, int k,
-                                             int32_t* __restrict__ out_index, float* __restrict__ out_d2) {
-    long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= nq) return;
-    const float* qp = queries + (size_t)q * dim;
+                                             int32_t* __restrict__ out_index, float* __restrict__ out_d2,
+                                             const int32_t* __restrict__ order) {
+    long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nq) return;
+    const long long q = order ? (long long)order[t] : t;
+    if (DIM > 0) dim = DIM;
+    RowOps<DIM> R;
+    R.load_query(queries + (size_t)q * dim, dim);
     unsigned st_lo[kMaxDepth], st_n[kMaxDepth];
     float st_da2[kMaxDepth];
-    unsigned char st_depth[kMaxDepth];
+    unsigned short st_axis[kMaxDepth];
     float bd[kMaxK];
     unsigned bs[kMaxK];
     int have = 0, sp = 0;
     unsigned lo = 0, cnt = N;
-    int depth = 0;
+    int axis = 0;
     for (;;) {
         while (cnt > 0) {
             unsigned m = cnt >> 1, slot = lo + m;
-            const float* pp = tp + (size_t)slot * dim;
-            int axis = depth % dim;
-            float de = dist2_exact(pp, qp, dim);
-            float da = __fsub_rn(qp[axis], pp[axis]);
+            float de, da;
+            R.visit(tp + (size_t)slot * dim, dim, axis, de, da);
             if (have < k || de < bd[have - 1]) {
                 int p = have < k ? have : k - 1;        // insertion, stable for equal distances
                 while (p > 0 && bd[p - 1] > de) { bd[p] = bd[p - 1]; bs[p] = bs[p - 1]; --p; }
@@ -430,18 +585,18 @@ __global__ void __launch_bounds__(128) k_knn(const float* __restrict__ tp, const
                 if (have < k) ++have;
             }
             unsigned rlo = slot + 1, rn = cnt - m - 1;
+            axis = axis + 1 == dim ? 0 : axis + 1;
             st_da2[sp] = __fmul_rn(da, da);
-            st_depth[sp] = (unsigned char)(depth + 1);
+            st_axis[sp] = (unsigned short)axis;
             if (da < 0.f) { st_lo[sp] = rlo; st_n[sp] = rn; cnt = m; }
             else { st_lo[sp] = lo; st_n[sp] = m; lo = rlo; cnt = rn; }
             ++sp;
-            ++depth;
         }
         bool resumed = false;
         while (sp > 0) {
             --sp;
             if (st_n[sp] > 0 && (have < k || st_da2[sp] < bd[have - 1])) {
-                lo = st_lo[sp]; cnt = st_n[sp]; depth = st_depth[sp];
+                lo = st_lo[sp]; cnt = st_n[sp]; axis = st_axis[sp];
                 resumed = true;
                 break;
             }
@@ -455,14 +610,21 @@ __global__ void __launch_bounds__(128) k_knn(const float* __restrict__ tp, const
 }
 }  // namespace kd
 
-extern "C" int kd_knn_gpu(const float* tree_points, const int32_t* perm, int64_t n, int dim, const float* queries,
-                          int64_t nq, int k, int32_t* out_index, float* out_dist2, void* stream) {
+extern "C" int kd_knn_ordered_gpu(const float* tree_points, const int32_t* perm, int64_t n, int dim, const float* queries,
+                                  int64_t nq, int k, const int32_t* order, int32_t* out_index, float* out_dist2,
+                                  void* stream) {
     if (!tree_points || !perm || !queries || !out_index || !out_dist2 || n <= 0 || dim <= 0 || nq < 0 || k < 1 ||
         k > kd::kMaxK || n >= (1ll << 31))
         return kd::fail("kd_knn_gpu: bad arguments (1 <= k <= 32)");
     if (nq == 0) return 0;
-    kd::k_knn<<<(unsigned)((nq + 127) / 128), 128, 0, (cudaStream_t)stream>>>(tree_points, perm, (unsigned)n, dim, queries,
-                                                                             nq, k, out_index, out_dist2);
+    const bool aligned = ((uintptr_t)tree_points & 15u) == 0;
+    KD_DIM_DISPATCH(dim, aligned, (kd::k_knn<D><<<(unsigned)((nq + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+        tree_points, perm, (unsigned)n, dim, queries, nq, k, out_index, out_dist2, order)));
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : kd::fail(std::string("kd_knn_gpu: ") + cudaGetErrorString(e));
+}
+
+extern "C" int kd_knn_gpu(const float* tree_points, const int32_t* perm, int64_t n, int dim, const float* queries,
+                          int64_t nq, int k, int32_t* out_index, float* out_dist2, void* stream) {
+    return kd_knn_ordered_gpu(tree_points, perm, n, dim, queries, nq, k, nullptr, out_index, out_dist2, stream);
 }

@@ -13,10 +13,10 @@ Reference parity: ``generate_uniform`` = Utility.cpp:6-18 / kdtree_mpi.cpp:19-41
 """
 from .generate import generate_clustered, generate_uniform, generate_problem
 from .build import build, build_workspace_bytes, build_into, last_launch_count, check_tree, build_cpu_sortref
-from .query import nearest, knn, gather_rows, materialize_nodes, bbox
+from .query import nearest, knn, gather_rows, materialize_nodes, bbox, query_order
 
 __all__ = [
     "generate_uniform", "generate_clustered", "generate_problem",
     "build", "build_into", "build_workspace_bytes", "last_launch_count", "check_tree", "build_cpu_sortref",
-    "nearest", "knn", "gather_rows", "materialize_nodes", "bbox",
+    "nearest", "knn", "gather_rows", "materialize_nodes", "bbox", "query_order",
 ]

@@ -14,6 +14,27 @@ from ._util import as_points, on_device, stream_ptr
 DENSE_MIN_DIM = int(os.environ.get("KD_B200_DENSE_MIN_DIM", "16"))
 
 
+# Batches of at least this many queries are grouped by the sub-tree they enter first before the DFS kernels run
+ORDER_MIN_QUERIES = int(os.environ.get("KD_B200_ORDER_MIN_QUERIES", "4096"))
+
+
+def query_order(tree_points: torch.Tensor, queries: torch.Tensor, levels: int | None = None) -> torch.Tensor:
+    """int32[nq] permutation that groups the queries by the sub-tree their search descends into first."""
+    n, dim = tree_points.shape
+    nq = queries.shape[0]
+    dev = tree_points.device
+    if levels is None:   # about 32 queries per group, never deeper than the tree
+        levels = max(1, min(16, (max(nq, 2) - 1).bit_length() - 5, max(1, n.bit_length() - 2)))
+    order = torch.empty(nq, dtype=torch.int32, device=dev)
+    key = torch.empty(nq, dtype=torch.int32, device=dev)
+    bins = torch.empty(1 << levels, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().kd_query_order_gpu(tree_points.data_ptr(), n, dim, queries.data_ptr(), nq, int(levels),
+                                       order.data_ptr(), key.data_ptr(), bins.data_ptr(), stream_ptr(dev)),
+              "kd::query_order")
+    return order
+
+
 def _nearest_op_impl(tree_points: torch.Tensor, perm: torch.Tensor, queries: torch.Tensor,
                      mode: str = "auto") -> tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
     tree_points = as_points(tree_points, "tree_points")
@@ -41,9 +62,11 @@ def _nearest_op_impl(tree_points: torch.Tensor, perm: torch.Tensor, queries: tor
                                                  nq, idx.data_ptr(), d2.data_ptr(), d.data_ptr(), vis.data_ptr(),
                                                  ws.data_ptr(), nbytes, stream_ptr(dev)), "kd::nearest")
             else:
-                check(lib().kd_nearest_gpu(tree_points.data_ptr(), perm.data_ptr(), n, dim, queries.data_ptr(), nq,
-                                           idx.data_ptr(), d2.data_ptr(), d.data_ptr(), vis.data_ptr(),
-                                           stream_ptr(dev)), "kd::nearest")
+                order = query_order(tree_points, queries) if nq >= ORDER_MIN_QUERIES else None
+                check(lib().kd_nearest_ordered_gpu(tree_points.data_ptr(), perm.data_ptr(), n, dim,
+                                                   queries.data_ptr(), nq, None if order is None else order.data_ptr(),
+                                                   idx.data_ptr(), d2.data_ptr(), d.data_ptr(), vis.data_ptr(),
+                                                   stream_ptr(dev)), "kd::nearest")
         vis = vis.long()
     else:
         # the CPU core indexes the original rows through perm; tree_points[s] == points[perm[s]]
@@ -167,9 +190,11 @@ def knn(tree_points: torch.Tensor, perm: torch.Tensor, queries: torch.Tensor, k:
     idx = torch.empty((nq, k), dtype=torch.int32, device=dev)
     d2 = torch.empty((nq, k), dtype=torch.float32, device=dev)
     if tree_points.is_cuda:
+        order = query_order(tree_points, queries) if nq >= ORDER_MIN_QUERIES else None
         with torch.cuda.device(dev):
-            check(lib().kd_knn_gpu(tree_points.data_ptr(), perm.data_ptr(), n, dim, queries.data_ptr(), nq, int(k),
-                                   idx.data_ptr(), d2.data_ptr(), stream_ptr(dev)), "kd::knn")
+            check(lib().kd_knn_ordered_gpu(tree_points.data_ptr(), perm.data_ptr(), n, dim, queries.data_ptr(), nq,
+                                           int(k), None if order is None else order.data_ptr(), idx.data_ptr(),
+                                           d2.data_ptr(), stream_ptr(dev)), "kd::knn")
     else:
         ident = torch.arange(n, dtype=torch.int32)
         slot = torch.empty((nq, k), dtype=torch.int32)

@@ -58,6 +58,21 @@ def test_ops_reject_or_move_foreign_tensors(kd):
         kd.ops.build_into(pts.cuda(), torch.empty(1000, dtype=torch.int32), None)     # perm on the wrong device
 
 
+def test_ordered_batches_give_the_same_answers(kd):
+    # >= 4096 queries: grouped by the sub-tree they enter first (own counting sort); results are order independent
+    pts, _ = kd.ops.generate_problem(3, 3, 300000, 0)
+    qs = kd.ops.generate_uniform(9, 3, 20000)
+    tc, tg = kd.KDTree(pts), kd.KDTree(pts.cuda())
+    order = kd.ops.query_order(tg.tree_points, qs.cuda())
+    assert torch.equal(order.long().sort().values.cpu(), torch.arange(20000))         # a permutation
+    cpu, res = tc.nearest(qs), tg.nearest(qs.cuda(), mode="dfs")
+    assert torch.equal(res.index.cpu(), cpu.index) and torch.equal(res.visited.cpu(), cpu.visited)
+    assert torch.equal(res.dist.cpu().view(torch.int32), cpu.dist.view(torch.int32))
+    ic, dc = kd.ops.knn(tc.tree_points, tc.perm, qs[:6000], 8)
+    ig, dg = kd.ops.knn(tg.tree_points, tg.perm, qs[:6000].cuda(), 8)
+    assert torch.equal(ig.cpu(), ic) and torch.equal(dg.cpu().view(torch.int32), dc.view(torch.int32))
+
+
 def test_default_problem_golden_lines_on_gpu(kd):
     # the graded problem (PDF p.4): 500000 x 128, seed 1; golden = unmodified ./sequential
     golden = ["707.539", "653.765", "693.995", "715.386", "732.924", "702.161", "739.194", "693.53", "698.66",
