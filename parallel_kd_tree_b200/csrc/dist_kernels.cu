@@ -1084,8 +1084,13 @@ __global__ void k_forest_min(ForestBuf* root, ForestBuf* mine, int rank, int wor
         // (peers poll their local `ready[0]`, which rank 0 cannot reach here, so they poll root->ready[rank])
         if (tid < world) st_release_sys(&root->ready[tid], epoch);
     } else {
-        if (tid == 0 && !wait_flag(&root->ready[rank], epoch)) atomicExch(err, 500);
+        __shared__ int s_ok;
+        if (tid == 0) {
+            s_ok = wait_flag(&root->ready[rank], epoch) ? 1 : 0;
+            if (!s_ok) atomicExch(err, 500);
+        }
         __syncthreads();
+        if (!s_ok) return;   // the accumulator may not be initialised: fold nothing into it, signal nothing
     }
     for (int q = tid; q < nq; q += blockDim.x) atomicMin_system(&root->val[q], __float_as_uint(dist[q]));
     __threadfence_system();

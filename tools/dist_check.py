@@ -17,9 +17,10 @@ os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
 dist.init_process_group("nccl", device_id=dev)
 ok = True
 for spec in (sys.argv[1:] or ["100003x3", "1048576x2", "4194304x3"]):
-    n, dim = (int(x) for x in spec.split("x"))
+    clustered = spec.startswith("clustered:")      # Gaussian blobs (BASELINE.json config 4): uneven exchange volumes
+    n, dim = (int(x) for x in spec.split(":")[-1].split("x"))
     first, local = kd.models.slice_bounds(n, world, rank)
-    pts = kd.ops.generate_uniform(5, dim, n)
+    pts = kd.ops.generate_clustered(5, dim, n) if clustered else kd.ops.generate_uniform(5, dim, n)
     db = IpcDistBuild(n, dim)
     if rank == 0:
         print(f"heap backend: symm={db._symm is not None} multicast={db.multicast}", flush=True)
