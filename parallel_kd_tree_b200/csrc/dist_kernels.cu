@@ -88,11 +88,11 @@ static DistLayout make_layout(int64_t n_total, int dim, int world, bool with_tp)
     L.max_rec = L.max_seg + kTargetCtas;
     L.st = take((size_t)L.max_seg * sizeof(SegState));
     L.ghist = take((size_t)L.max_seg * kDigitBins * 4);
-    L.lrec = take((size_t)L.max_rec * sizeof(MaxRec));
+    L.lrec = take((size_t)(L.max_rec + 8 * kTargetCtas) * sizeof(MaxRec));   // (+ room for 8 concurrent slices)
     L.lerr = take(256);
     L.ckey = take((size_t)L.cap * 4);
     L.cidx = take((size_t)L.cap * 4);
-    L.ccta = take((size_t)L.max_rec * 4);
+    L.ccta = take((size_t)(L.max_rec + 8 * kTargetCtas) * 4);
     L.bytes = off;
     return L;
 }
@@ -791,8 +791,10 @@ __global__ void __launch_bounds__(512) k_replicate(const int32_t* __restrict__ p
     }
 }
 
-// side stream + events of the overlapped replication, one set per device
-struct SideStream { cudaStream_t s; cudaEvent_t ev[8]; bool ok; };
+// streams + events of the sliced local phase, one set per device: slice c is built and replicated on stream c,
+// earlier slices have the higher priority, so they finish first and their replication runs next to the others' work
+constexpr int kMaxSlices = 8;
+struct SideStream { cudaStream_t s[kMaxSlices]; cudaEvent_t fork, join[kMaxSlices]; bool ok; };
 static int side_stream(SideStream** out) {
     static std::mutex mu;
     static SideStream tab[64] = {};
@@ -801,9 +803,15 @@ static int side_stream(SideStream** out) {
     std::lock_guard<std::mutex> lock(mu);
     SideStream& S = tab[dev];
     if (!S.ok) {
-        if (cudaStreamCreateWithFlags(&S.s, cudaStreamNonBlocking) != cudaSuccess) return fail("kd_dist: cudaStreamCreate failed");
-        for (auto& e : S.ev)
-            if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return fail("kd_dist: cudaEventCreate failed");
+        int least = 0, greatest = 0;
+        cudaDeviceGetStreamPriorityRange(&least, &greatest);   // numerically lower = higher priority
+        for (int c = 0; c < kMaxSlices; ++c) {
+            const int prio = std::max(greatest, std::min(least, greatest + c));
+            if (cudaStreamCreateWithPriority(&S.s[c], cudaStreamNonBlocking, prio) != cudaSuccess)
+                return fail("kd_dist: cudaStreamCreateWithPriority failed");
+            if (cudaEventCreateWithFlags(&S.join[c], cudaEventDisableTiming) != cudaSuccess) return fail("kd_dist: cudaEventCreate failed");
+        }
+        if (cudaEventCreateWithFlags(&S.fork, cudaEventDisableTiming) != cudaSuccess) return fail("kd_dist: cudaEventCreate failed");
         S.ok = true;
     }
     *out = &S;
@@ -811,11 +819,9 @@ static int side_stream(SideStream** out) {
 }
 
 constexpr unsigned kChunkMinLocal = 1u << 21;  // the local phase is finished in slices when a GPU holds at least this many points
-// 1 << chunk_level() slices (KD_DIST_CHUNK_LEVEL).  Default 0 = off: measured on 8 B200 at 2^28 x 3 the sliced local
-// phase LOSES (19.3 ms unsliced, 21.5 ms with 2 slices, 23.1 ms with 4): every slice repeats the latency-bound top
-// levels (~17 dependent launches per level), which costs more than the hidden link time (profiles/ROOFLINE.md).
+// 1 << chunk_level() slices (KD_DIST_CHUNK_LEVEL; 0 = the whole slice at once, stores replicated by the kernels themselves)
 static int chunk_level() {
-    static const int v = [] { const char* e = std::getenv("KD_DIST_CHUNK_LEVEL"); int x = e ? std::atoi(e) : 0; return x < 0 ? 0 : (x > 3 ? 3 : x); }();
+    static const int v = [] { const char* e = std::getenv("KD_DIST_CHUNK_LEVEL"); int x = e ? std::atoi(e) : 2; return x < 0 ? 0 : (x > 3 ? 3 : x); }();
     return v;
 }
 
@@ -865,9 +871,10 @@ static int local_build(const HostCtx& H, cudaStream_t st) {
 
     // Overlap of the sub-tree all-gather with the local phase: the top kChunkLevel local levels run on the whole
     // slice (their few nodes go to every replica directly); then the slice is finished range by range into this
-    // GPU's OWN tree arrays, and every finished range is pushed to the peers on a side stream while the next range
-    // is being built.  3.3 GB arrive at every GPU in an 8-GPU build of 2^28 x 3: >= 4.3 ms of link time that used
-    // to follow the local phase now run next to it.
+    // GPU's OWN tree arrays, every range on a stream of its own (own scratch), earlier ranges at higher priority.
+    // The ranges fill each other's launch-latency gaps, finish one after the other, and each is pushed to the peers
+    // (k_replicate) on its stream while the later ones are still being built.  3.3 GB arrive at every GPU in an
+    // 8-GPU build of 2^28 x 3: >= 4.3 ms of link time that used to follow the local phase.
     SideStream* S = nullptr;
     if (int rc = side_stream(&S)) return rc;
     int cur = L & 1;
@@ -876,7 +883,12 @@ static int local_build(const HostCtx& H, cudaStream_t st) {
     own.n = 1;
     own.perm[0] = (int32_t*)(base + P.L.perm);
     own.tp[0] = H.with_tp ? (float*)(base + P.L.tp) : nullptr;
-    for (unsigned c = 0; c < (1u << kChunkLevel); ++c) {
+    if (cudaEventRecord(S->fork, st) != cudaSuccess) return fail("kd_dist_local_build: cudaEventRecord failed");
+    const unsigned nslice = 1u << kChunkLevel;
+    const size_t seg_per = (size_t)std::max<int64_t>(1, P.L.max_seg >> kChunkLevel), rec_per = seg_per + kTargetCtas;
+    for (unsigned c = 0; c < nslice; ++c) {
+        cudaStream_t sc_st = S->s[c];
+        if (cudaStreamWaitEvent(sc_st, S->fork, 0) != cudaSuccess) return fail("kd_dist_local_build: cudaStreamWaitEvent failed");
         unsigned clo, cn;
         host_seg_range(n, kChunkLevel, c, clo, cn);
         Cols sb[2];
@@ -884,15 +896,20 @@ static int local_build(const HostCtx& H, cudaStream_t st) {
             for (int k = 0; k < kMaxCarry; ++k) sb[b].c[k] = buf[b].c[k] ? buf[b].c[k] + clo : nullptr;
             sb[b].idx = buf[b].idx + clo;
         }
-        if (int rc = build_core(sb, cur, (int64_t)cn, P.dim, P.ncol, L + kChunkLevel, lo + clo, own, nullptr, sc, st, -1, nullptr))
+        BuildScratch s2 = sc;   // private select state per slice (the slices run concurrently)
+        s2.st = sc.st + c * seg_per;
+        s2.ghist = sc.ghist + c * seg_per * kDigitBins;
+        s2.rec = sc.rec + c * rec_per;
+        s2.cand_cta = sc.cand_cta + c * rec_per;
+        s2.cand_key = sc.cand_key + clo;
+        s2.cand_idx = sc.cand_idx + clo;
+        if (int rc = build_core(sb, cur, (int64_t)cn, P.dim, P.ncol, L + kChunkLevel, lo + clo, own, nullptr, s2, sc_st, -1, nullptr))
             return rc;
-        if (cudaEventRecord(S->ev[c], st) != cudaSuccess || cudaStreamWaitEvent(S->s, S->ev[c], 0) != cudaSuccess)
-            return fail("kd_dist_local_build: event hand-over to the replication stream failed");
-        k_replicate<<<96, 512, 0, S->s>>>(own.perm[0], own.tp[0], rep, (size_t)lo + clo, (size_t)cn, P.dim);
+        k_replicate<<<64, 512, 0, sc_st>>>(own.perm[0], own.tp[0], rep, (size_t)lo + clo, (size_t)cn, P.dim);
         KD_DLAUNCH("k_replicate");
+        if (cudaEventRecord(S->join[c], sc_st) != cudaSuccess || cudaStreamWaitEvent(st, S->join[c], 0) != cudaSuccess)
+            return fail("kd_dist_local_build: joining a slice stream failed");
     }
-    if (cudaEventRecord(S->ev[7], S->s) != cudaSuccess || cudaStreamWaitEvent(st, S->ev[7], 0) != cudaSuccess)
-        return fail("kd_dist_local_build: joining the replication stream failed");
     return 0;
 }
 
