@@ -229,6 +229,14 @@ __global__ void k_bracket_finish(SegState* st, unsigned N, int level, unsigned n
         st[s].use_cand = 1;
         st[s].rank = m - cL;
         st[s].cnt = cc;
+        // every candidate lies in [lowP, highP]: the bits the two pivots share are resolved already, so the first
+        // digit pass starts right below them instead of re-counting eleven bits that cannot differ
+        const unsigned long long lowP = st[s].lowP, highP = st[s].highP;
+        if (lowP != 0ull && highP != ~0ull && lowP != highP) {
+            const int hi = 64 - __clzll((long long)(lowP ^ highP));
+            st[s].shift = hi;
+            st[s].prefix = hi >= 64 ? 0ull : ((lowP >> hi) << hi);
+        }
     }
 }
 
@@ -276,13 +284,15 @@ __global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys_a
     }
     for (int t = threadIdx.x; t < kDigitBins; t += BLOCK) sh[t] = 0;
     __syncthreads();
-    const int dsh = digit_shift(d);
-    const unsigned mask = (1u << digit_bits(d)) - 1u;
+    // bits [hi, 64) of the composite are resolved; this pass counts the digit right below them (at most 11 bits,
+    // never straddling the key | index boundary)
+    const int hi = S.shift, dsh = select_digit_shift(hi);
+    const unsigned mask = (1u << (hi - dsh)) - 1u;
     const unsigned iters = (e - b + BLOCK * UNROLL - 1) / (BLOCK * UNROLL);
-    if (d < 3) {
-        const int ks = dsh - 32;
-        const int ps = d == 0 ? 0 : digit_shift(d - 1) - 32;
-        const unsigned want = d == 0 ? 0u : (unsigned)(S.prefix >> digit_shift(d - 1));
+    (void)d;
+    if (hi > 32) {
+        const int ks = dsh - 32, ps = hi - 32;
+        const unsigned want = hi >= 64 ? 0u : (unsigned)(S.prefix >> hi);
         for (unsigned it = 0; it < iters; ++it) {
             unsigned i0 = b + it * (BLOCK * UNROLL) + threadIdx.x;
             float f[UNROLL];
@@ -292,14 +302,13 @@ __global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys_a
             for (int u = 0; u < UNROLL; ++u) {
                 bool valid = (i0 + u * BLOCK) < e;
                 unsigned key = ordered_key(f[u]);
-                if (d > 0) valid = valid && ((key >> ps) == want);
+                if (hi < 64) valid = valid && ((key >> ps) == want);
                 warp_hist_add(sh, (key >> ks) & mask, valid);
             }
         }
     } else {
         const unsigned wantkey = (unsigned)(S.prefix >> 32);
-        const int ps = d == 3 ? 0 : digit_shift(d - 1);
-        const unsigned wantidx = d == 3 ? 0u : ((unsigned)(S.prefix & 0xffffffffull) >> ps);
+        const unsigned wantidx = hi >= 32 ? 0u : ((unsigned)(S.prefix & 0xffffffffull) >> hi);
         for (unsigned it = 0; it < iters; ++it) {
             unsigned i0 = b + it * (BLOCK * UNROLL) + threadIdx.x;
             float f[UNROLL];
@@ -310,7 +319,7 @@ __global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys_a
                 unsigned i = i0 + u * BLOCK;
                 bool valid = i < e && ordered_key(f[u]) == wantkey;
                 unsigned id = valid ? point_index(i) : 0u;
-                if (d > 3) valid = valid && ((id >> ps) == wantidx);
+                if (hi < 32) valid = valid && ((id >> hi) == wantidx);
                 warp_hist_add(sh, (id >> dsh) & mask, valid);
             }
         }
@@ -364,11 +373,12 @@ __global__ void __launch_bounds__(256) k_scan(SegState* st, unsigned* ghist, int
             atomicExch(err, 1 + d);  // the histogram does not contain the wanted rank: internal error
             S.done = 1;
         } else {
-            S.prefix |= (unsigned long long)(unsigned)fbin << digit_shift(d);
+            const int dsh = select_digit_shift(S.shift);
+            S.prefix |= (unsigned long long)(unsigned)fbin << dsh;
             S.rank = r - fcum;
             S.cnt = fcnt;
-            S.shift = digit_shift(d);
-            S.done = d == kNumDigits - 1 ? 1 : (fcnt == 1u ? (S.use_cand ? 2 : 1) : 0);
+            S.shift = dsh;
+            S.done = dsh == 0 ? 1 : (fcnt == 1u ? (S.use_cand ? 2 : 1) : 0);
         }
         st[s] = S;
     }

@@ -26,6 +26,7 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -818,6 +819,10 @@ static int side_stream(SideStream** out) {
     return 0;
 }
 
+static int replicate_grid() {   // CTAs of k_replicate (KD_DIST_REP_GRID)
+    static const int v = [] { const char* e = std::getenv("KD_DIST_REP_GRID"); int x = e ? std::atoi(e) : 64; return x < 1 ? 1 : x; }();
+    return v;
+}
 constexpr unsigned kChunkMinLocal = 1u << 21;  // the local phase is finished in slices when a GPU holds at least this many points
 // 1 << chunk_level() slices (KD_DIST_CHUNK_LEVEL; 0 = the whole slice at once, stores replicated by the kernels themselves)
 static int chunk_level() {
@@ -885,6 +890,13 @@ static int local_build(const HostCtx& H, cudaStream_t st) {
     own.tp[0] = H.with_tp ? (float*)(base + P.L.tp) : nullptr;
     if (cudaEventRecord(S->fork, st) != cudaSuccess) return fail("kd_dist_local_build: cudaEventRecord failed");
     const unsigned nslice = 1u << kChunkLevel;
+    // KD_DIST_TRACE=1: timed events per slice, printed (with a device synchronisation) at the end of the call
+    static const bool trace = std::getenv("KD_DIST_TRACE") != nullptr;
+    cudaEvent_t tev[2 * kMaxSlices + 1] = {};
+    if (trace) {
+        for (auto& e : tev) cudaEventCreate(&e);
+        cudaEventRecord(tev[2 * kMaxSlices], st);
+    }
     const size_t seg_per = (size_t)std::max<int64_t>(1, P.L.max_seg >> kChunkLevel), rec_per = seg_per + kTargetCtas;
     for (unsigned c = 0; c < nslice; ++c) {
         cudaStream_t sc_st = S->s[c];
@@ -905,10 +917,26 @@ static int local_build(const HostCtx& H, cudaStream_t st) {
         s2.cand_idx = sc.cand_idx + clo;
         if (int rc = build_core(sb, cur, (int64_t)cn, P.dim, P.ncol, L + kChunkLevel, lo + clo, own, nullptr, s2, sc_st, -1, nullptr))
             return rc;
-        k_replicate<<<64, 512, 0, sc_st>>>(own.perm[0], own.tp[0], rep, (size_t)lo + clo, (size_t)cn, P.dim);
+        if (trace) cudaEventRecord(tev[2 * c], sc_st);
+        k_replicate<<<replicate_grid(), 512, 0, sc_st>>>(own.perm[0], own.tp[0], rep, (size_t)lo + clo, (size_t)cn, P.dim);
         KD_DLAUNCH("k_replicate");
+        if (trace) cudaEventRecord(tev[2 * c + 1], sc_st);
         if (cudaEventRecord(S->join[c], sc_st) != cudaSuccess || cudaStreamWaitEvent(st, S->join[c], 0) != cudaSuccess)
             return fail("kd_dist_local_build: joining a slice stream failed");
+    }
+    if (trace) {
+        cudaDeviceSynchronize();
+        std::string line = "[kd trace] rank " + std::to_string(P.rank) + " slices (ms after the fork: built / replicated):";
+        for (unsigned c = 0; c < nslice; ++c) {
+            float a = 0.f, b = 0.f;
+            cudaEventElapsedTime(&a, tev[2 * kMaxSlices], tev[2 * c]);
+            cudaEventElapsedTime(&b, tev[2 * kMaxSlices], tev[2 * c + 1]);
+            char buf2[64];
+            snprintf(buf2, sizeof buf2, " %.2f/%.2f", a, b);
+            line += buf2;
+        }
+        fprintf(stderr, "%s\n", line.c_str());
+        for (auto& e : tev) cudaEventDestroy(e);
     }
     return 0;
 }

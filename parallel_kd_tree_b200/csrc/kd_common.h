@@ -54,5 +54,8 @@ constexpr int kNumDigits = 6;
 constexpr int kDigitBins = 2048;
 KD_HD int digit_shift(int d) { return d == 0 ? 53 : d == 1 ? 42 : d == 2 ? 32 : d == 3 ? 21 : d == 4 ? 10 : 0; }
 KD_HD int digit_bits(int d) { return (d == 2 || d == 5) ? 10 : 11; }
+// Single-GPU select: bits [hi, 64) of the composite are resolved; the next digit is the (at most) 11 bits below
+// them and never straddles the key | index boundary at bit 32.  From hi = 64 this is the schedule above.
+KD_HD int select_digit_shift(int hi) { return hi > 32 ? (hi - 11 > 32 ? hi - 11 : 32) : (hi - 11 > 0 ? hi - 11 : 0); }
 
 }  // namespace kd
