@@ -145,6 +145,9 @@ int kd_dist_init(const kd_dist_ctx* ctx, const float* local_points, int64_t loca
 int kd_dist_run(const kd_dist_ctx* ctx, uint64_t serial, void* stream);
 /* the same build phase by phase, for W virtual ranks driven by one process (posts of all ranks before waits) */
 int kd_dist_phase(const kd_dist_ctx* ctx, int level, int phase, int pass, uint64_t serial, void* stream);
+/* the (phase, pass) pairs of one distributed level in launch order (sample bracket, digit passes, counts, partition,
+ * left-maximum fix-up); drivers of virtual ranks launch each pair for every rank before the next pair */
+int kd_dist_schedule(int* phases, int* passes, int cap);
 int kd_dist_local_build(const kd_dist_ctx* ctx, void* stream);
 int kd_dist_done(const kd_dist_ctx* ctx, int post, uint64_t serial, void* stream);
 /* synchronises the stream; non-zero if a device-side check or a peer wait failed */

@@ -40,7 +40,10 @@
 namespace kd {
 
 constexpr int kMaxWorld = 8;
-enum FlagKind { F_HIST = 0, F_CNT, F_PART, F_MAX, F_FIX, F_DONE, kNumFlagKinds };
+enum FlagKind { F_HIST = 0, F_CNT, F_PART, F_MAX, F_FIX, F_DONE, F_SAMP, F_BRK, kNumFlagKinds };
+constexpr int kDSample = 1024;          // sample composites per rank per distributed level
+constexpr int kRedStride = kDigitBins + 32;   // one NVLS accumulator: the bins + its arrival counter (+ padding)
+constexpr int kRedPasses = 8;
 
 struct DistCtl {
     unsigned long long prefix;
@@ -53,13 +56,20 @@ struct DistCtl {
     unsigned curL, curR;   // local partition cursors
     unsigned ticket;       // last-CTA election of k_hist_dist
     int err;
+    // sample bracket (all members derive the same pivots from the union of the ranks' samples)
+    unsigned cL;           // local elements below lowP
+    unsigned cand_cnt;     // local candidates (lowP <= composite <= highP), compacted to the candidate arrays
+    int use_cand;          // 1: the digit passes run on the candidates
+    unsigned long long lowP, highP;
+    unsigned bticket;      // last-CTA election of k_dbracket
     unsigned pad[3];
 };
 
 struct MaxSlot { unsigned long long comp; unsigned off; unsigned valid; };
 
 struct DistLayout {
-    size_t ctl, flags, hist_slots, lhist, cnt_slots, max_slots, rec, col[2][kMaxCarry], idx[2], perm, tp;
+    size_t ctl, flags, hist_slots, lhist, own_hist, samp_slots, brk_slots, racc, cnt_slots, max_slots, rec, col[2][kMaxCarry],
+        idx[2], perm, tp;
     size_t st, ghist, lrec, lerr, ckey, cidx, ccta;  // scratch of the local (single-GPU) phase
     size_t bytes;
     int64_t cap, max_seg, max_rec;
@@ -74,6 +84,11 @@ static DistLayout make_layout(int64_t n_total, int dim, int world, bool with_tp)
     L.flags = take(sizeof(unsigned long long) * kNumFlagKinds * kMaxWorld);
     L.hist_slots = take((size_t)2 * kMaxWorld * kDigitBins * 4);
     L.lhist = take((size_t)kDigitBins * 4);
+    L.own_hist = take((size_t)2 * kDigitBins * 4);
+    L.samp_slots = take((size_t)kMaxWorld * kDSample * 8);
+    L.brk_slots = take((size_t)kMaxWorld * 4 * 4);
+    // NVLS accumulators of the histogram reduction: [build parity][level 0: 1 | level 1: 2 | level 2: 4 groups][pass]
+    L.racc = take((size_t)2 * 7 * kRedPasses * kRedStride * 4);
     L.cnt_slots = take((size_t)kMaxWorld * 4 * 4);
     L.max_slots = take(sizeof(MaxSlot) * kMaxWorld);
     L.rec = take(sizeof(MaxRec) * (size_t)(kTargetCtas + 8));
@@ -139,13 +154,47 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
     asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+// Peer waits give up after kWaitBudgetNs of WALL time (the global nanosecond timer, independent of the SM clock) and
+// report an error instead of hanging the device; every kernel that follows a failed wait returns at once (ctl->err).
+constexpr unsigned long long kWaitBudgetNs = 10ull * 1000 * 1000 * 1000;   // 10 s: far beyond any lazy module load or peer mapping
 __device__ __forceinline__ bool wait_flag(const unsigned long long* p, unsigned long long epoch) {
-    const long long t0 = clock64();
+    const unsigned long long t0 = global_ns();
     while (ld_acquire_sys(p) < epoch) {
-        if (clock64() - t0 > 4000000000ll) return false;  // ~2 s: give up, never hang the device
+        if (global_ns() - t0 > kWaitBudgetNs) return false;
         __nanosleep(64);
     }
     return true;
+}
+__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ bool wait_count(const unsigned* p, unsigned want) {
+    const unsigned long long t0 = global_ns();
+    while (ld_acquire_sys_u32(p) < want) {
+        if (global_ns() - t0 > kWaitBudgetNs) return false;
+        __nanosleep(64);
+    }
+    return true;
+}
+// NVLS: one reduction store on the multicast address adds `v` into the same word of every GPU's heap (the switch
+// fans it out); the release form orders this thread's earlier multicast reductions before it at every destination.
+__device__ __forceinline__ void multimem_red_add(unsigned* mc, unsigned v) {
+    asm volatile("multimem.red.relaxed.sys.global.add.u32 [%0], %1;" ::"l"(mc), "r"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_red_add_release(unsigned* mc, unsigned v) {
+    asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(mc), "r"(v) : "memory");
+}
+// accumulator of (build parity, level, group, pass) inside a heap (byte offset)
+__host__ __device__ inline size_t racc_off(const DistLayout& L, unsigned parity, int level, int group, int pass) {
+    const int area = (level == 0 ? 0 : level == 1 ? 1 : 3) + group;
+    return L.racc + ((size_t)(parity * 7 + area) * kRedPasses + (size_t)pass) * kRedStride * 4;
 }
 
 #define DCTL(P, r) (reinterpret_cast<DistCtl*>((P).heap[r] + (P).L.ctl))
@@ -198,7 +247,207 @@ __global__ void k_dist_state_init(DistParams P, LevelGeo g) {
     c->mine = 0;
     c->curL = c->curR = 0;
     c->ticket = 0;
+    c->cL = 0;
+    c->cand_cnt = 0;
+    c->use_cand = 0;
+    c->lowP = 0ull;
+    c->highP = ~0ull;
+    c->bticket = 0;
     if (g.level > 0) c->cnt = share_of(g.n, (unsigned)g.G, (unsigned)g.j);
+}
+
+// ---- K5, sample bracket across the group ----
+// Every member posts a sorted systematic sample of its keys to all members (one-shot P2P stores); every member then
+// ranks the union and picks the same two pivots around the wanted rank; ONE pass over the local keys counts what
+// lies below the bracket and compacts what lies inside it (a few per cent); the digit passes run on those
+// candidates, starting below the bits the pivots share.  Exact: the counts prove whether the rank is inside the
+// bracket, otherwise the level falls back to digit passes over all keys.
+__global__ void __launch_bounds__(512) k_dsample(DistParams P, LevelGeo g, int cur, int axis, unsigned long long epoch) {
+    __shared__ unsigned long long sm[kDSample];
+    DistCtl* ctl = DCTL(P, P.rank);
+    if (ctl->err) return;
+    const unsigned local_n = ctl->cnt, tid = threadIdx.x;
+    const unsigned free_n = (g.j == g.G - 1) ? local_n - 1u : local_n;
+    const Cols src = cols_of(P, P.rank, cur);
+    for (unsigned k = tid; k < (unsigned)kDSample; k += 512) {
+        const unsigned pos = (unsigned)(((unsigned long long)k * free_n) / kDSample);
+        sm[k] = composite(ordered_key(src.c[axis][pos]), (unsigned)src.idx[pos]);
+    }
+    __syncthreads();
+    for (unsigned k = 2; k <= (unsigned)kDSample; k <<= 1)
+        for (unsigned j = k >> 1; j > 0; j >>= 1) {
+            const unsigned i = ((tid & ~(j - 1u)) << 1) | (tid & (j - 1u)), l = i | j;
+            const bool asc = (i & k) == 0u;
+            const unsigned long long a = sm[i], b = sm[l];
+            if ((a > b) == asc) { sm[i] = b; sm[l] = a; }
+            __syncthreads();
+        }
+    for (int m = 0; m < g.G; ++m) {
+        unsigned long long* slot = reinterpret_cast<unsigned long long*>(P.heap[g.gb + m] + P.L.samp_slots) + (size_t)g.j * kDSample;
+        for (unsigned k = tid; k < (unsigned)kDSample; k += 512) slot[k] = sm[k];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if ((int)tid < g.G) st_release_sys(DFLAG(P, g.gb + tid, F_SAMP, g.j), epoch);
+}
+
+__device__ __forceinline__ unsigned lower_bound_u64(const unsigned long long* a, unsigned n, unsigned long long x) {
+    unsigned lo = 0, hi = n;
+    while (lo < hi) {
+        const unsigned mid = (lo + hi) >> 1;
+        if (a[mid] < x) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(1024) k_dpivots(DistParams P, LevelGeo g, unsigned long long epoch) {
+    extern __shared__ __align__(16) unsigned char pv_smem[];
+    unsigned long long* all = reinterpret_cast<unsigned long long*>(pv_smem);   // [G][kDSample] sorted lists
+    __shared__ unsigned long long s_low, s_high;
+    DistCtl* ctl = DCTL(P, P.rank);
+    const unsigned tid = threadIdx.x;
+    if (ctl->err) return;
+    if ((int)tid < g.G) {
+        if (!wait_flag(DFLAG(P, P.rank, F_SAMP, tid), epoch)) atomicExch(&ctl->err, 600);
+    }
+    if (tid == 0) { s_low = 0ull; s_high = ~0ull; }
+    __syncthreads();
+    if (ctl->err) return;
+    const unsigned S = (unsigned)g.G * kDSample;
+    const unsigned long long* slots = reinterpret_cast<const unsigned long long*>(P.heap[P.rank] + P.L.samp_slots);
+    for (unsigned e = tid; e < S; e += 1024) all[e] = __ldcg(&slots[e]);
+    __syncthreads();
+    const unsigned m = g.n >> 1, free_total = g.n - 1u;
+    const long long R = (long long)(((unsigned long long)m * S) / free_total);
+    const long long delta = g.G >= 8 ? 204 : g.G >= 4 ? 144 : g.G >= 2 ? 102 : 72;   // 72 * sqrt(G): 4.5 sigma of a sample rank
+    const long long rlo = R - delta, rhi = R + delta;
+    for (unsigned e = tid; e < S; e += 1024) {
+        const unsigned l = e / kDSample, i = e % kDSample;
+        const unsigned long long x = all[e];
+        long long rank = i;                        // rank of x in the union = elements below it in every list
+        for (int l2 = 0; l2 < g.G; ++l2)
+            if ((unsigned)l2 != l) rank += lower_bound_u64(all + (size_t)l2 * kDSample, kDSample, x);
+        if (rank <= rlo) atomicMax(&s_low, x);
+        if (rank >= rhi) atomicMin(&s_high, x);
+    }
+    __syncthreads();
+    if (tid == 0) { ctl->lowP = s_low; ctl->highP = s_high; }
+}
+
+template <int BLOCK, int IPT>
+__global__ void __launch_bounds__(BLOCK) k_dbracket(DistParams P, LevelGeo g, int cur, int axis, unsigned long long epoch) {
+    __shared__ unsigned s_cur, s_less;
+    __shared__ int s_last;
+    DistCtl* ctl = DCTL(P, P.rank);
+    if (ctl->err) return;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const unsigned long long lowP = ctl->lowP, highP = ctl->highP;
+    const unsigned lowK = (unsigned)(lowP >> 32), highK = (unsigned)(highP >> 32);
+    auto key_float = [](unsigned k) { return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k); };
+    const float lowF = lowP == 0ull ? __int_as_float(0xff800000) : key_float(lowK);
+    const float highF = highP == ~0ull ? __int_as_float(0x7f800000) : key_float(highK);
+    const unsigned local_n = ctl->cnt;
+    const unsigned free_n = (g.j == g.G - 1) ? local_n - 1u : local_n;
+    const Cols src = cols_of(P, P.rank, cur);
+    const float* __restrict__ keys = src.c[axis];
+    const int32_t* __restrict__ idx = src.idx;
+    float* __restrict__ cand_key = reinterpret_cast<float*>(P.heap[P.rank] + P.L.ckey);
+    int32_t* __restrict__ cand_idx = reinterpret_cast<int32_t*>(P.heap[P.rank] + P.L.cidx);
+    unsigned* __restrict__ cand_cta = reinterpret_cast<unsigned*>(P.heap[P.rank] + P.L.ccta);
+    const unsigned chunk = (free_n + gridDim.x - 1) / gridDim.x;
+    const unsigned b = min(blockIdx.x * chunk, free_n), e = min(b + chunk, free_n);
+    unsigned less = 0;
+    if (tid == 0) { s_cur = 0; s_less = 0; }
+    __syncthreads();
+    for (unsigned tb = b; tb < e; tb += BLOCK * IPT) {
+        float f[IPT];
+#pragma unroll
+        for (int k = 0; k < IPT; ++k) {
+            const unsigned i = tb + k * BLOCK + tid;
+            f[k] = i < e ? keys[i] : __int_as_float(0x7fc00000);
+        }
+        unsigned cmask = 0;
+#pragma unroll
+        for (int k = 0; k < IPT; ++k) {
+            const float v = f[k];
+            if (v < lowF) ++less;
+            else if (v <= highF) {
+                bool cand = true;
+                if (v == lowF || v == highF) {
+                    const unsigned i = tb + k * BLOCK + tid;
+                    const unsigned long long c = composite(ordered_key(v), (unsigned)idx[i]);
+                    if (c < lowP) { ++less; cand = false; }
+                    else cand = c <= highP;
+                }
+                cmask |= cand ? (1u << k) : 0u;
+            }
+        }
+        const unsigned mine = __popc(cmask);
+        unsigned inc = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        const unsigned total = __shfl_sync(0xffffffffu, inc, 31);
+        unsigned base = 0;
+        if (lane == 31 && total) base = atomicAdd(&s_cur, total);
+        base = __shfl_sync(0xffffffffu, base, 31);
+        unsigned p = b + base + inc - mine;
+#pragma unroll
+        for (int k = 0; k < IPT; ++k)
+            if (cmask & (1u << k)) {
+                cand_key[p] = f[k];
+                cand_idx[p] = (int32_t)(tb + k * BLOCK + tid);
+                ++p;
+            }
+    }
+    for (int o = 16; o > 0; o >>= 1) less += __shfl_xor_sync(0xffffffffu, less, o);
+    if (lane == 0 && less) atomicAdd(&s_less, less);
+    __syncthreads();
+    if (tid == 0) {
+        cand_cta[blockIdx.x] = s_cur;
+        if (s_cur) atomicAdd(&ctl->cand_cnt, s_cur);
+        if (s_less) atomicAdd(&ctl->cL, s_less);
+        __threadfence();
+        s_last = atomicAdd(&ctl->bticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    if (tid < g.G) {   // my (below, inside) counts -> every member, one-shot
+        unsigned* slot = reinterpret_cast<unsigned*>(P.heap[g.gb + tid] + P.L.brk_slots) + g.j * 4;
+        slot[0] = __ldcg(&ctl->cL);
+        slot[1] = __ldcg(&ctl->cand_cnt);
+        __threadfence_system();
+        st_release_sys(DFLAG(P, g.gb + tid, F_BRK, g.j), epoch);
+    }
+}
+
+__global__ void k_dbracket_wait(DistParams P, LevelGeo g, unsigned long long epoch) {
+    DistCtl* ctl = DCTL(P, P.rank);
+    if (ctl->err) return;
+    if ((int)threadIdx.x < g.G) {
+        if (!wait_flag(DFLAG(P, P.rank, F_BRK, threadIdx.x), epoch)) atomicExch(&ctl->err, 610);
+    }
+    __syncthreads();
+    if (threadIdx.x || ctl->err) return;
+    const unsigned* slots = reinterpret_cast<const unsigned*>(P.heap[P.rank] + P.L.brk_slots);
+    unsigned cL = 0, cc = 0;
+    for (int m = 0; m < g.G; ++m) { cL += __ldcg(&slots[m * 4]); cc += __ldcg(&slots[m * 4 + 1]); }
+    const unsigned m = g.n >> 1;
+    if (m >= cL && m - cL < cc) {   // the wanted rank is inside the bracket on the union of the members' counts
+        ctl->use_cand = 1;
+        ctl->rank_wanted = m - cL;
+        ctl->cnt_global = cc;
+        ctl->my_less = ctl->cL;
+        const unsigned long long lowP = ctl->lowP, highP = ctl->highP;
+        if (lowP != 0ull && highP != ~0ull && lowP != highP) {
+            const int hi = 64 - __clzll((long long)(lowP ^ highP));
+            ctl->shift = hi;
+            ctl->prefix = hi >= 64 ? 0ull : ((lowP >> hi) << hi);
+        }
+    }
 }
 
 // K5 (post side): local histogram of digit d; the last CTA to finish publishes the rank's bins to every
@@ -210,24 +459,28 @@ __device__ __forceinline__ void warp_hist_add_d(unsigned* sh, unsigned digit, bo
 
 template <int BLOCK, int UNROLL>
 __global__ void __launch_bounds__(BLOCK) k_hist_dist(DistParams P, LevelGeo g, int cur, int axis, int d,
-                                                     unsigned long long epoch) {
+                                                     unsigned long long epoch, unsigned parity) {
     __shared__ unsigned sh[kDigitBins];
     __shared__ int s_last;
     DistCtl* ctl = DCTL(P, P.rank);
-    if (ctl->done) return;
+    if (ctl->done || ctl->err) return;
     const unsigned long long prefix = ctl->prefix;
     const unsigned local_n = ctl->cnt;
     const unsigned free_n = (g.j == g.G - 1) ? local_n - 1u : local_n;  // the range's pinned last element sits on the last member
     const Cols src = cols_of(P, P.rank, cur);
-    const float* __restrict__ keys = src.c[axis];
+    const bool via = ctl->use_cand != 0;   // after a successful bracket: the compacted candidates of this CTA's chunk
+    const float* __restrict__ keys = via ? reinterpret_cast<const float*>(P.heap[P.rank] + P.L.ckey) : src.c[axis];
+    const int32_t* __restrict__ cand_idx = reinterpret_cast<const int32_t*>(P.heap[P.rank] + P.L.cidx);
     const int32_t* __restrict__ idx = src.idx;
     const unsigned chunk = (free_n + gridDim.x - 1) / gridDim.x;
-    const unsigned b = min(blockIdx.x * chunk, free_n), e = min(b + chunk, free_n);
+    const unsigned b = min(blockIdx.x * chunk, free_n);
+    const unsigned e = via ? b + reinterpret_cast<const unsigned*>(P.heap[P.rank] + P.L.ccta)[blockIdx.x] : min(b + chunk, free_n);
     for (int t = threadIdx.x; t < kDigitBins; t += BLOCK) sh[t] = 0;
     __syncthreads();
-    const int dsh = digit_shift(d);
-    const unsigned mask = (1u << digit_bits(d)) - 1u;
-    const unsigned iters = (e - b + BLOCK * UNROLL - 1) / (BLOCK * UNROLL);
+    // bits [hi, 64) of the composite are resolved; this pass counts the (at most 11-bit) digit right below them
+    const int hi = ctl->shift, dsh = select_digit_shift(hi);
+    const unsigned mask = (1u << (hi - dsh)) - 1u;
+    const unsigned iters = e > b ? (e - b + BLOCK * UNROLL - 1) / (BLOCK * UNROLL) : 0u;
     const unsigned wantkey = (unsigned)(prefix >> 32);
     for (unsigned it = 0; it < iters; ++it) {
         unsigned i0 = b + it * (BLOCK * UNROLL) + threadIdx.x;
@@ -240,13 +493,13 @@ __global__ void __launch_bounds__(BLOCK) k_hist_dist(DistParams P, LevelGeo g, i
             bool valid = i < e;
             const unsigned key = ordered_key(f[u]);
             unsigned digit;
-            if (d < 3) {
-                if (d > 0) valid = valid && ((key >> (digit_shift(d - 1) - 32)) == (unsigned)(prefix >> digit_shift(d - 1)));
+            if (hi > 32) {
+                if (hi < 64) valid = valid && ((key >> (hi - 32)) == (unsigned)(prefix >> hi));
                 digit = (key >> (dsh - 32)) & mask;
             } else {
                 valid = valid && key == wantkey;
-                const unsigned id = valid ? (unsigned)idx[i] : 0u;
-                if (d > 3) valid = valid && ((id >> digit_shift(d - 1)) == ((unsigned)(prefix & 0xffffffffull) >> digit_shift(d - 1)));
+                const unsigned id = valid ? (unsigned)(via ? idx[cand_idx[i]] : idx[i]) : 0u;
+                if (hi < 32) valid = valid && ((id >> hi) == ((unsigned)(prefix & 0xffffffffull) >> hi));
                 digit = (id >> dsh) & mask;
             }
             warp_hist_add_d(sh, digit, valid);
@@ -264,10 +517,28 @@ __global__ void __launch_bounds__(BLOCK) k_hist_dist(DistParams P, LevelGeo g, i
     __syncthreads();
     if (!s_last) return;
     __threadfence();
-    // one-shot reduction: my bins go to slot (d & 1, my member index) of every member, then their flag
+    // The last CTA publishes the rank's bins.  NVLS: ONE multimem.red per non-empty bin adds it into the group's
+    // accumulator on every GPU (the switch performs the reduction's fan-out), then one release-ordered reduction
+    // bumps the accumulator's arrival counter.  Without a multicast mapping: one-shot slot stores to every member.
+    unsigned* own = reinterpret_cast<unsigned*>(P.heap[P.rank] + P.L.own_hist) + (size_t)(d & 1) * kDigitBins;
+    if (P.mc) {
+        unsigned* acc = reinterpret_cast<unsigned*>(P.mc + racc_off(P.L, parity, g.level, P.rank / g.G, d));
+        for (int t = threadIdx.x; t < kDigitBins; t += BLOCK) {
+            const unsigned v = __ldcg(&lh[t]);
+            lh[t] = 0;
+            own[t] = v;
+            if (v) multimem_red_add(acc + t, v);
+        }
+        if (threadIdx.x == 0) ctl->ticket = 0;
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) multimem_red_add_release(acc + kDigitBins, 1u);
+        return;
+    }
     for (int t = threadIdx.x; t < kDigitBins; t += BLOCK) {
         const unsigned v = __ldcg(&lh[t]);
         lh[t] = 0;
+        own[t] = v;
         for (int m = 0; m < g.G; ++m) {
             unsigned* slot = reinterpret_cast<unsigned*>(P.heap[g.gb + m] + P.L.hist_slots) +
                              ((size_t)(d & 1) * kMaxWorld + g.j) * kDigitBins;
@@ -280,28 +551,34 @@ __global__ void __launch_bounds__(BLOCK) k_hist_dist(DistParams P, LevelGeo g, i
     if ((int)threadIdx.x < g.G) st_release_sys(DFLAG(P, g.gb + threadIdx.x, F_HIST, g.j), epoch);
 }
 
-// K5 (wait side): sum the members' slots, locate the bin of the wanted rank, extend the prefix.
-__global__ void __launch_bounds__(256) k_scan_dist(DistParams P, LevelGeo g, int d, unsigned long long epoch) {
+// K5 (wait side): the summed bins (NVLS accumulator, or the members' slots), the bin of the wanted rank, the prefix.
+__global__ void __launch_bounds__(256) k_scan_dist(DistParams P, LevelGeo g, int d, unsigned long long epoch, unsigned parity) {
     __shared__ unsigned wsum[8];
     __shared__ int fbin;
     __shared__ unsigned fcum, fcnt, s_own_less, s_own_at;
     DistCtl* ctl = DCTL(P, P.rank);
-    if (ctl->done) return;
+    if (ctl->done || ctl->err) return;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     if (tid == 0) { fbin = -1; s_own_less = 0; s_own_at = 0; }
-    if (tid < g.G) {
+    const unsigned* acc = reinterpret_cast<const unsigned*>(P.heap[P.rank] + racc_off(P.L, parity, g.level, P.rank / g.G, d));
+    if (P.mc) {
+        if (tid == 0 && !wait_count(acc + kDigitBins, (unsigned)g.G)) atomicExch(&ctl->err, 100 + d);
+    } else if (tid < g.G) {
         if (!wait_flag(DFLAG(P, P.rank, F_HIST, tid), epoch)) atomicExch(&ctl->err, 100 + d);
     }
     __syncthreads();
+    if (ctl->err) return;
     const unsigned* slots = reinterpret_cast<const unsigned*>(P.heap[P.rank] + P.L.hist_slots) +
                             (size_t)(d & 1) * kMaxWorld * kDigitBins;
+    const unsigned* ownh = reinterpret_cast<const unsigned*>(P.heap[P.rank] + P.L.own_hist) + (size_t)(d & 1) * kDigitBins;
     unsigned v[8], own[8], sum = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
         unsigned a = 0;
-        for (int m = 0; m < g.G; ++m) a += __ldcg(&slots[(size_t)m * kDigitBins + tid * 8 + k]);
+        if (P.mc) a = __ldcg(&acc[tid * 8 + k]);
+        else for (int m = 0; m < g.G; ++m) a += __ldcg(&slots[(size_t)m * kDigitBins + tid * 8 + k]);
         v[k] = a;
-        own[k] = __ldcg(&slots[(size_t)g.j * kDigitBins + tid * 8 + k]);
+        own[k] = __ldcg(&ownh[tid * 8 + k]);
         sum += a;
     }
     unsigned inc = sum;
@@ -337,12 +614,15 @@ __global__ void __launch_bounds__(256) k_scan_dist(DistParams P, LevelGeo g, int
             atomicExch(&ctl->err, 1 + d);
             ctl->done = 1;
         } else {
-            ctl->prefix |= (unsigned long long)(unsigned)fb << digit_shift(d);
+            const int dsh = select_digit_shift(ctl->shift);
+            ctl->prefix |= (unsigned long long)(unsigned)fb << dsh;
             ctl->rank_wanted = r - fcum;
             ctl->cnt_global = fcnt;
-            ctl->shift = digit_shift(d);
+            ctl->shift = dsh;
             ctl->my_less += s_own_less;
-            if (fcnt == 1u || d == kNumDigits - 1) { ctl->done = 1; ctl->mine = s_own_at; }
+            // one element left (inside the bracket, if there is one): the partition tells it from the elements
+            // outside the bracket that share its resolved bits by comparing with the pivots first
+            if (fcnt == 1u || dsh == 0) { ctl->done = 1; ctl->mine = s_own_at; }
         }
     }
 }
@@ -350,6 +630,7 @@ __global__ void __launch_bounds__(256) k_scan_dist(DistParams P, LevelGeo g, int
 // per-rank left/right counts -> every member (post), then exclusive scan over members (wait)
 __global__ void k_counts_post(DistParams P, LevelGeo g, unsigned long long epoch) {
     DistCtl* ctl = DCTL(P, P.rank);
+    if (ctl->err) return;
     const unsigned local_n = ctl->cnt;
     const unsigned free_n = (g.j == g.G - 1) ? local_n - 1u : local_n;
     const unsigned lc = ctl->my_less, rc = free_n - lc - ctl->mine;
@@ -364,6 +645,7 @@ __global__ void k_counts_post(DistParams P, LevelGeo g, unsigned long long epoch
 
 __global__ void k_counts_wait(DistParams P, LevelGeo g, unsigned long long epoch) {
     DistCtl* ctl = DCTL(P, P.rank);
+    if (ctl->err) return;
     if ((int)threadIdx.x < g.G) {
         if (!wait_flag(DFLAG(P, P.rank, F_CNT, threadIdx.x), epoch)) atomicExch(&ctl->err, 200);
     }
@@ -393,10 +675,13 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
     __shared__ unsigned long long s_wcomp[BLOCK / 32];
     __shared__ unsigned s_wpos[BLOCK / 32];
     DistCtl* ctl = DCTL(P, P.rank);
+    if (ctl->err) return;   // a peer wait failed earlier: the counts below cannot be trusted, store nothing anywhere
     const int tid = threadIdx.x, lane = tid & 31;
     const unsigned long long prefix = ctl->prefix;
     const int shift = ctl->shift;
-    const unsigned long long want = prefix >> shift;
+    const unsigned long long want = shift >= 64 ? 0ull : (prefix >> shift);
+    const bool bracketed = ctl->use_cand != 0;
+    const unsigned long long lowP = bracketed ? ctl->lowP : 0ull, highP = bracketed ? ctl->highP : ~0ull;
     const unsigned local_n = ctl->cnt;
     const bool last_member = g.j == g.G - 1;
     const unsigned free_n = last_member ? local_n - 1u : local_n;
@@ -448,8 +733,10 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
             key[k] = ordered_key(kf);
             side[k] = 2;
             if (i < e) {
-                unsigned long long c = composite(key[k], (unsigned)id[k]) >> shift;
-                side[k] = c < want ? -1 : (c > want ? 1 : 0);
+                const unsigned long long cf = composite(key[k], (unsigned)id[k]);
+                const unsigned long long c = cf >> shift;
+                // outside the bracket the pivots decide (such elements may share the node's resolved high bits)
+                side[k] = cf < lowP ? -1 : (cf > highP ? 1 : (c < want ? -1 : (c > want ? 1 : 0)));
             }
         }
 #pragma unroll
@@ -578,6 +865,7 @@ __global__ void __launch_bounds__(256) k_max_post(DistParams P, LevelGeo g, int 
     __shared__ unsigned long long s_c[8];
     __shared__ unsigned s_p[8], s_v[8];
     const MaxRec* rec = reinterpret_cast<const MaxRec*>(P.heap[P.rank] + P.L.rec);
+    if (DCTL(P, P.rank)->err) return;
     unsigned long long best = 0ull;
     unsigned bestpos = 0, bestvalid = 0;
     for (int t = threadIdx.x; t < nrec; t += blockDim.x) {
@@ -606,10 +894,12 @@ __global__ void __launch_bounds__(256) k_max_post(DistParams P, LevelGeo g, int 
 // Wait: the owner of the left child's last slot exchanges it with the winner.
 __global__ void k_max_wait_swap(DistParams P, LevelGeo g, int cur, unsigned long long epoch) {
     DistCtl* ctl = DCTL(P, P.rank);
+    if (ctl->err) return;
     if ((int)threadIdx.x < g.G) {
         if (!wait_flag(DFLAG(P, P.rank, F_MAX, threadIdx.x), epoch)) atomicExch(&ctl->err, 400);
     }
     __syncthreads();
+    if (ctl->err) return;
     const unsigned m = g.n >> 1, Gh = (unsigned)g.G >> 1;
     unsigned lastmem, lastpos;
     owner_of(m - 1u, m, Gh, lastmem, lastpos);
@@ -666,14 +956,49 @@ static LevelGeo make_geo(const DistParams& P, int level) {
     } while (0)
 
 enum Phase { PH_STATE = 0, PH_HIST, PH_SCAN, PH_CNT_POST, PH_CNT_WAIT, PH_PART, PH_PART_POST, PH_PART_WAIT, PH_MAX_POST,
-             PH_MAX_WAIT, PH_FIX_POST, PH_FIX_WAIT, kNumPhases };
+             PH_MAX_WAIT, PH_FIX_POST, PH_FIX_WAIT, PH_SAMPLE_POST, PH_PIVOT_WAIT, PH_BRACKET_POST, PH_BRACKET_WAIT,
+             kNumPhases };
+
+// One distributed level in launch order: (phase, pass) pairs.  Drivers of virtual ranks launch every entry for all
+// ranks before the next entry (posts before waits); kd_dist_run walks the same list for its own rank.
+struct Step { int phase, pass; };
+static int level_schedule(Step* out) {
+    int n = 0;
+    out[n++] = {PH_STATE, 0};
+    out[n++] = {PH_SAMPLE_POST, 6};
+    out[n++] = {PH_PIVOT_WAIT, 6};
+    out[n++] = {PH_BRACKET_POST, 5};
+    out[n++] = {PH_BRACKET_WAIT, 5};
+    for (int d = 0; d < kNumDigits; ++d) { out[n++] = {PH_HIST, d}; out[n++] = {PH_SCAN, d}; }
+    for (int ph = PH_CNT_POST; ph <= PH_FIX_WAIT; ++ph) out[n++] = {ph, 7};
+    return n;
+}
 
 static int dist_grid(unsigned local_n, int min_chunk) {
     int64_t cap = std::max<int64_t>(1, ((int64_t)local_n + min_chunk - 1) / min_chunk);
     return (int)std::min<int64_t>(kTargetCtas, cap);
 }
 
+// opt-in shared-memory sizes of the distributed kernels, once per device, every result checked
+static int dist_func_attributes_once() {
+    static std::mutex mu;
+    static bool done[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail(std::string("kd_dist: cudaGetDevice: ") + cudaGetErrorString(e));
+    std::lock_guard<std::mutex> lock(mu);
+    if (dev >= 0 && dev < 64 && done[dev]) return 0;
+    e = cudaFuncSetAttribute(k_dpivots, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxWorld * kDSample * 8);
+#define KD_PD_ATTR(NC) if (e == cudaSuccess) e = cudaFuncSetAttribute(k_partition_dist<NC, 512, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ((NC) + 1) * 2048 * 4)
+    KD_PD_ATTR(1); KD_PD_ATTR(2); KD_PD_ATTR(3); KD_PD_ATTR(4); KD_PD_ATTR(5); KD_PD_ATTR(6); KD_PD_ATTR(7); KD_PD_ATTR(8);
+#undef KD_PD_ATTR
+    if (e != cudaSuccess) return fail(std::string("kd_dist: cudaFuncSetAttribute: ") + cudaGetErrorString(e));
+    if (dev >= 0 && dev < 64) done[dev] = true;
+    return 0;
+}
+
 static int run_phase(const HostCtx& H, int level, int phase, int pass, unsigned long long serial, cudaStream_t st) {
+    if (int rc = dist_func_attributes_once()) return rc;
     const DistParams& P = H.P;
     const LevelGeo g = make_geo(P, level);
     const int cur = level & 1;
@@ -681,17 +1006,41 @@ static int run_phase(const HostCtx& H, int level, int phase, int pass, unsigned 
     const unsigned long long epoch = serial * 64ull + (unsigned long long)level * 8ull + (unsigned long long)pass + 1ull;
     // upper bound of my local count at this level (the device reads the exact value from its control block)
     const unsigned local_cap = (unsigned)H.P.L.cap;
+    const unsigned parity = (unsigned)(serial & 1ull);
     switch (phase) {
         case PH_STATE:
+            if (level == 0 && P.mc) {
+                // NVLS accumulators of the NEXT build (other parity): the build that used them last is complete on
+                // every rank (its done-barrier precedes this build), the next build starts after this one's barrier
+                if (cudaMemsetAsync(P.heap[P.rank] + racc_off(P.L, parity ^ 1u, 0, 0, 0), 0,
+                                    (size_t)7 * kRedPasses * kRedStride * 4, st) != cudaSuccess)
+                    return fail("kd_dist_phase: cudaMemsetAsync failed");
+            }
             k_dist_state_init<<<1, 32, 0, st>>>(P, g);
             KD_DLAUNCH("k_dist_state_init");
             break;
+        case PH_SAMPLE_POST:
+            k_dsample<<<1, 512, 0, st>>>(P, g, cur, axis, epoch);
+            KD_DLAUNCH("k_dsample");
+            break;
+        case PH_PIVOT_WAIT:
+            k_dpivots<<<1, 1024, (size_t)g.G * kDSample * 8, st>>>(P, g, epoch);
+            KD_DLAUNCH("k_dpivots");
+            break;
+        case PH_BRACKET_POST:   // same grid as the digit passes: they read the candidates chunk by chunk
+            k_dbracket<512, 8><<<dist_grid(local_cap, 8192), 512, 0, st>>>(P, g, cur, axis, epoch);
+            KD_DLAUNCH("k_dbracket");
+            break;
+        case PH_BRACKET_WAIT:
+            k_dbracket_wait<<<1, 32, 0, st>>>(P, g, epoch);
+            KD_DLAUNCH("k_dbracket_wait");
+            break;
         case PH_HIST:
-            k_hist_dist<512, 4><<<dist_grid(local_cap, 16384), 512, 0, st>>>(P, g, cur, axis, pass, epoch);
+            k_hist_dist<512, 4><<<dist_grid(local_cap, 8192), 512, 0, st>>>(P, g, cur, axis, pass, epoch, parity);
             KD_DLAUNCH("k_hist_dist");
             break;
         case PH_SCAN:
-            k_scan_dist<<<1, 256, 0, st>>>(P, g, pass, epoch);
+            k_scan_dist<<<1, 256, 0, st>>>(P, g, pass, epoch, parity);
             KD_DLAUNCH("k_scan_dist");
             break;
         case PH_CNT_POST:
@@ -707,7 +1056,6 @@ static int run_phase(const HostCtx& H, int level, int phase, int pass, unsigned 
 #define KD_PD(NC)                                                                                              \
     do {                                                                                                       \
         const size_t sm = (size_t)((NC) + 1) * 2048 * 4;                                                       \
-        cudaFuncSetAttribute(k_partition_dist<NC, 512, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm); \
         k_partition_dist<NC, 512, 4><<<grid, 512, sm, st>>>(P, g, cur, axis, H.with_tp);                       \
     } while (0)
             switch (P.ncol) {
@@ -1028,18 +1376,23 @@ int kd_dist_run(const kd_dist_ctx* ctx, uint64_t serial, void* stream) {
     if (int rc = fill_ctx(ctx, H)) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     const int L = kd::dist_levels(H.P.world);
-    for (int level = 0; level < L; ++level) {
-        if (int rc = kd::run_phase(H, level, kd::PH_STATE, 0, serial, st)) return rc;
-        for (int d = 0; d < kd::kNumDigits; ++d) {
-            if (int rc = kd::run_phase(H, level, kd::PH_HIST, d, serial, st)) return rc;
-            if (int rc = kd::run_phase(H, level, kd::PH_SCAN, d, serial, st)) return rc;
-        }
-        for (int ph = kd::PH_CNT_POST; ph < kd::kNumPhases; ++ph)
-            if (int rc = kd::run_phase(H, level, ph, 7, serial, st)) return rc;
-    }
+    kd::Step steps[64];
+    const int ns = kd::level_schedule(steps);
+    for (int level = 0; level < L; ++level)
+        for (int k = 0; k < ns; ++k)
+            if (int rc = kd::run_phase(H, level, steps[k].phase, steps[k].pass, serial, st)) return rc;
     if (int rc = kd::local_build(H, st)) return rc;
     if (int rc = kd_dist_done(ctx, 1, serial, stream)) return rc;
     return kd_dist_done(ctx, 0, serial, stream);
+}
+
+/* the (phase, pass) pairs of one distributed level in launch order; returns their number (<= cap) */
+int kd_dist_schedule(int* phases, int* passes, int cap) {
+    kd::Step steps[64];
+    const int ns = kd::level_schedule(steps);
+    if (!phases || !passes || cap < ns) return kd::fail("kd_dist_schedule: need room for " + std::to_string(ns) + " steps"), -1;
+    for (int k = 0; k < ns; ++k) { phases[k] = steps[k].phase; passes[k] = steps[k].pass; }
+    return ns;
 }
 
 int kd_dist_status(const kd_dist_ctx* ctx, void* stream) {

@@ -21,9 +21,16 @@ from .._lib import DistCtx, KdError, check, lib
 from ..models.forest import slice_bounds
 
 PH_STATE, PH_HIST, PH_SCAN, PH_CNT_POST, PH_CNT_WAIT, PH_PART, PH_PART_POST, PH_PART_WAIT, PH_MAX_POST, \
-    PH_MAX_WAIT, PH_FIX_POST, PH_FIX_WAIT = range(12)
-_NUM_DIGITS = 6
-_NOPASS = 7
+    PH_MAX_WAIT, PH_FIX_POST, PH_FIX_WAIT, PH_SAMPLE_POST, PH_PIVOT_WAIT, PH_BRACKET_POST, PH_BRACKET_WAIT = range(16)
+
+
+def level_schedule() -> list[tuple[int, int]]:
+    """(phase, pass) pairs of one distributed level in launch order, as the native library defines them."""
+    ph, ps = (C.c_int * 64)(), (C.c_int * 64)()
+    n = lib().kd_dist_schedule(ph, ps, 64)
+    if n < 0:
+        raise KdError("kd_dist_schedule failed")
+    return [(int(ph[i]), int(ps[i])) for i in range(n)]
 
 
 def _levels(world: int) -> int:
@@ -101,13 +108,10 @@ class EmulatedDistBuild(_Base):
                 for ctx in self.ctxs:
                     check(L.kd_dist_phase(C.byref(ctx), level, ph, p, self.serial, st), "kd_dist_phase")
 
+            steps = level_schedule()
             for level in range(_levels(self.world)):
-                phase(level, PH_STATE, 0)
-                for d in range(_NUM_DIGITS):
-                    phase(level, PH_HIST, d)
-                    phase(level, PH_SCAN, d)
-                for ph in range(PH_CNT_POST, PH_FIX_WAIT + 1):
-                    phase(level, ph, _NOPASS)
+                for ph, ps in steps:          # every step for all ranks before the next one (posts before waits)
+                    phase(level, ph, ps)
             for ctx in self.ctxs:
                 check(L.kd_dist_local_build(C.byref(ctx), st), "kd_dist_local_build")
             for post in (1, 0):

@@ -1,7 +1,8 @@
 """Per-level timing of the distributed build's fused paths (BASELINE.json config 5: "per-level exchange GB/s
 sweep against 900 GB/s per direction").  torchrun --nproc-per-node W tools/exchange_sweep.py [log2n] [dim]
 
-For every distributed level: device time of the select (histogram passes + one-shot P2P reduction + scans) and
+For every distributed level: device time of the select (sample bracket, digit passes over the candidates, the
+histograms reduced through NVLS multimem.red or one-shot P2P slots, scans, count exchange) and
 of the partition-to-peer kernel, the bytes that kernel pushes over NVLink from this GPU, and the resulting
 GB/s per direction per GPU.  Then the local phase (whose stores are replicated into every GPU = the all-gather).
 Times are max over ranks (CUDA events)."""
@@ -31,6 +32,7 @@ b = db.IpcDistBuild(n, dim, with_tree_points=True)
 L = kd.lib()
 st = torch.cuda.current_stream().cuda_stream
 levels = world.bit_length() - 1
+steps = db.level_schedule()
 
 
 def ev():
@@ -43,17 +45,12 @@ def run(record):
     for level in range(levels):
         e0, e1, e2, e3 = ev(), ev(), ev(), ev()
         e0.record()
-        kd._lib.check(L.kd_dist_phase(C.byref(b.ctx), level, db.PH_STATE, 0, b.serial, st), "state")
-        for d in range(6):
-            kd._lib.check(L.kd_dist_phase(C.byref(b.ctx), level, db.PH_HIST, d, b.serial, st), "hist")
-            kd._lib.check(L.kd_dist_phase(C.byref(b.ctx), level, db.PH_SCAN, d, b.serial, st), "scan")
-        for ph in (db.PH_CNT_POST, db.PH_CNT_WAIT):
-            kd._lib.check(L.kd_dist_phase(C.byref(b.ctx), level, ph, 7, b.serial, st), "cnt")
-        e1.record()
-        kd._lib.check(L.kd_dist_phase(C.byref(b.ctx), level, db.PH_PART, 7, b.serial, st), "part")
-        e2.record()
-        for ph in range(db.PH_PART_POST, db.PH_FIX_WAIT + 1):
-            kd._lib.check(L.kd_dist_phase(C.byref(b.ctx), level, ph, 7, b.serial, st), "sync")
+        for ph, ps in steps:       # select = everything before the partition kernel; sync/fix-up = everything after it
+            if ph == db.PH_PART:
+                e1.record()
+            kd._lib.check(L.kd_dist_phase(C.byref(b.ctx), level, ph, ps, b.serial, st), "phase")
+            if ph == db.PH_PART:
+                e2.record()
         e3.record()
         record.append((level, e0, e1, e2, e3))
     e4, e5 = ev(), ev()
