@@ -459,7 +459,7 @@ __device__ __forceinline__ void warp_hist_add_d(unsigned* sh, unsigned digit, bo
 
 template <int BLOCK, int UNROLL>
 __global__ void __launch_bounds__(BLOCK) k_hist_dist(DistParams P, LevelGeo g, int cur, int axis, int d,
-                                                     unsigned long long epoch, unsigned parity) {
+                                                     unsigned long long epoch, unsigned parity, unsigned nchunk) {
     __shared__ unsigned sh[kDigitBins];
     __shared__ int s_last;
     DistCtl* ctl = DCTL(P, P.rank);
@@ -472,16 +472,19 @@ __global__ void __launch_bounds__(BLOCK) k_hist_dist(DistParams P, LevelGeo g, i
     const float* __restrict__ keys = via ? reinterpret_cast<const float*>(P.heap[P.rank] + P.L.ckey) : src.c[axis];
     const int32_t* __restrict__ cand_idx = reinterpret_cast<const int32_t*>(P.heap[P.rank] + P.L.cidx);
     const int32_t* __restrict__ idx = src.idx;
-    const unsigned chunk = (free_n + gridDim.x - 1) / gridDim.x;
-    const unsigned b = min(blockIdx.x * chunk, free_n);
-    const unsigned e = via ? b + reinterpret_cast<const unsigned*>(P.heap[P.rank] + P.L.ccta)[blockIdx.x] : min(b + chunk, free_n);
+    // the keys are cut into `nchunk` chunks (the geometry k_dbracket compacted the candidates with); a CTA walks
+    // several of them, so that the fixed cost of a pass (clearing and flushing 2048 bins) is paid by few CTAs
+    const unsigned chunk = (free_n + nchunk - 1) / nchunk;
     for (int t = threadIdx.x; t < kDigitBins; t += BLOCK) sh[t] = 0;
     __syncthreads();
     // bits [hi, 64) of the composite are resolved; this pass counts the (at most 11-bit) digit right below them
     const int hi = ctl->shift, dsh = select_digit_shift(hi);
     const unsigned mask = (1u << (hi - dsh)) - 1u;
-    const unsigned iters = e > b ? (e - b + BLOCK * UNROLL - 1) / (BLOCK * UNROLL) : 0u;
     const unsigned wantkey = (unsigned)(prefix >> 32);
+    for (unsigned ck = blockIdx.x; ck < nchunk; ck += gridDim.x) {
+    const unsigned b = min(ck * chunk, free_n);
+    const unsigned e = via ? b + reinterpret_cast<const unsigned*>(P.heap[P.rank] + P.L.ccta)[ck] : min(b + chunk, free_n);
+    const unsigned iters = e > b ? (e - b + BLOCK * UNROLL - 1) / (BLOCK * UNROLL) : 0u;
     for (unsigned it = 0; it < iters; ++it) {
         unsigned i0 = b + it * (BLOCK * UNROLL) + threadIdx.x;
         float f[UNROLL];
@@ -504,6 +507,7 @@ __global__ void __launch_bounds__(BLOCK) k_hist_dist(DistParams P, LevelGeo g, i
             }
             warp_hist_add_d(sh, digit, valid);
         }
+    }
     }
     __syncthreads();
     unsigned* lh = reinterpret_cast<unsigned*>(P.heap[P.rank] + P.L.lhist);
@@ -1036,7 +1040,10 @@ static int run_phase(const HostCtx& H, int level, int phase, int pass, unsigned 
             KD_DLAUNCH("k_dbracket_wait");
             break;
         case PH_HIST:
-            k_hist_dist<512, 4><<<dist_grid(local_cap, 8192), 512, 0, st>>>(P, g, cur, axis, pass, epoch, parity);
+            {   // full-key passes need every SM; passes over the candidates are tiny
+                const int nchunk = dist_grid(local_cap, 8192);
+                k_hist_dist<512, 4><<<std::min(nchunk, 296), 512, 0, st>>>(P, g, cur, axis, pass, epoch, parity, (unsigned)nchunk);
+            }
             KD_DLAUNCH("k_hist_dist");
             break;
         case PH_SCAN:
