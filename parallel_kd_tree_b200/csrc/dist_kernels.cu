@@ -983,6 +983,15 @@ static int dist_grid(unsigned local_n, int min_chunk) {
     return (int)std::min<int64_t>(kTargetCtas, cap);
 }
 
+// CTA width of k_partition_dist (KD_DIST_PART_BLOCK = 128 | 512).  128-thread CTAs with 512-point tiles: many
+// independent tiles per SM hide each tile's load -> rank -> claim (a global atomic round trip) -> stage -> push chain
+// (measured on 2 B200, 2^25 points per GPU: 0.68 ms with 128 threads, 0.98 ms with 512; unstaged stores straight
+// from the registers, two short runs per warp instruction, were slower than either over the link: 0.95 ms)
+static int part_block() {
+    static const int v = [] { const char* e = std::getenv("KD_DIST_PART_BLOCK"); int x = e ? std::atoi(e) : 128; return x == 512 ? 512 : 128; }();
+    return v;
+}
+
 // opt-in shared-memory sizes of the distributed kernels, once per device, every result checked
 static int dist_func_attributes_once() {
     static std::mutex mu;
@@ -1060,10 +1069,13 @@ static int run_phase(const HostCtx& H, int level, int phase, int pass, unsigned 
             break;
         case PH_PART: {
             const int grid = dist_grid(local_cap, 2048);
+            const int pblock = part_block();
 #define KD_PD(NC)                                                                                              \
     do {                                                                                                       \
-        const size_t sm = (size_t)((NC) + 1) * 2048 * 4;                                                       \
-        k_partition_dist<NC, 512, 4><<<grid, 512, sm, st>>>(P, g, cur, axis, H.with_tp);                       \
+        if (pblock == 128)                                                                                     \
+            k_partition_dist<NC, 128, 4><<<grid, 128, (size_t)((NC) + 1) * 512 * 4, st>>>(P, g, cur, axis, H.with_tp);  \
+        else                                                                                                   \
+            k_partition_dist<NC, 512, 4><<<grid, 512, (size_t)((NC) + 1) * 2048 * 4, st>>>(P, g, cur, axis, H.with_tp); \
     } while (0)
             switch (P.ncol) {
                 case 1: KD_PD(1); break;
