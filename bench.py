@@ -264,6 +264,9 @@ def run_ours(args) -> dict:
     total_ms = sum(a.elapsed_time(b) for a, b in evs)
     clocks = sampler.stop()
     ms_per_step = total_ms / args.steps
+    # the device-side error word of the last timed build (a select that lost its rank raises here)
+    from parallel_kd_tree_b200._lib import check as _check
+    _check(kd.lib().kd_build_status(ws.data_ptr(), n, dim, torch.cuda.current_stream().cuda_stream), "kd::build (timed steps)")
 
     # End to end through the public API: every step copies its points from pinned host memory to the device,
     # builds, and copies the finished tree (perm) back to pinned host memory.  Consecutive steps are pipelined

@@ -148,6 +148,9 @@ int kd_dist_phase(const kd_dist_ctx* ctx, int level, int phase, int pass, uint64
 /* the (phase, pass) pairs of one distributed level in launch order (sample bracket, digit passes, counts, partition,
  * left-maximum fix-up); drivers of virtual ranks launch each pair for every rank before the next pair */
 int kd_dist_schedule(int* phases, int* passes, int cap);
+/* synchronises the stream; out[8] = this rank's counters of the level that ran last: local count, elements going left,
+ * holds-the-node flag, first left / right output offset, elements below the bracket, candidates, bracket-used flag */
+int kd_dist_level_counts(const kd_dist_ctx* ctx, uint32_t* out, void* stream);
 int kd_dist_local_build(const kd_dist_ctx* ctx, void* stream);
 int kd_dist_done(const kd_dist_ctx* ctx, int post, uint64_t serial, void* stream);
 /* synchronises the stream; non-zero if a device-side check or a peer wait failed */

@@ -55,7 +55,7 @@ def run(args, kd, dist, rank, world, dev, sampler_cls, baseline_pps):
 
     # End to end: every step uploads this rank's slice from pinned host memory, runs the distributed build and
     # downloads this rank's share of perm.  Steps are pipelined like a stream of requests: double-buffered
-    # input slices, the result staged device-to-device, copies on their own streams.
+    # input slices, the result snapshotted device-to-device, copies on their own streams.
     pts2 = [local_pts, torch.empty_like(local_pts)]
     stage2 = [torch.empty(local, dtype=torch.int32, device=dev) for _ in range(2)]
     host_perm2 = [host_perm, torch.empty(local, dtype=torch.int32, pin_memory=True)]
@@ -77,6 +77,8 @@ def run(args, kd, dist, rank, world, dev, sampler_cls, baseline_pps):
                 main.wait_event(ev_d2h[i - 2])
             db.load(pts2[b])
             db.run()
+            # 0.1 ms device-to-device snapshot of this rank's share: the next build overwrites the tree arrays while
+            # the 134 MB download (7 ms when eight ranks share the host's PCIe, profiles/h2d_probe_8gpu.json) is in flight
             stage2[b].copy_(db.perm[first:first + local])
             ev_build[i] = torch.cuda.Event()
             ev_build[i].record(main)
@@ -101,6 +103,20 @@ def run(args, kd, dist, rank, world, dev, sampler_cls, baseline_pps):
     dist.all_reduce(lo, op=dist.ReduceOp.MIN)
     dist.all_reduce(hi, op=dist.ReduceOp.MAX)
     consistent = bool(torch.equal(lo, hi)) and int(chk[0].item()) == n * (n - 1) // 2
+    # The RIGHT tree, not only a consistent one: rank 0 builds the same points on its own GPU alone and compares the
+    # two permutations element by element (the other ranks' replicas are tied to rank 0's by the checksums above).
+    matches = None
+    if os.environ.get("KD_BENCH_SKIP_TREE_CHECK") != "1":
+        db.status()
+        if rank == 0:
+            full = (kd.ops.generate_clustered(args.seed, dim, n) if args.dist == "clustered"
+                    else kd.ops.generate_uniform(args.seed, dim, n)).to(dev)
+            ref_perm = torch.empty(n, dtype=torch.int32, device=dev)
+            ws = torch.empty(kd.ops.build_workspace_bytes(n, dim), dtype=torch.uint8, device=dev)
+            kd.ops.build_into(full, ref_perm, None, ws, verify=True)
+            matches = bool(torch.equal(ref_perm, db.perm))
+            del full, ref_perm, ws
+        dist.barrier()
     value = n / (ms_per_step * 1e-3)
     out = {
         "metric": "kd-tree build points/sec", "value": value, "unit": "points/s", "n_gpus": world, "steps": args.steps,
@@ -113,7 +129,7 @@ def run(args, kd, dist, rank, world, dev, sampler_cls, baseline_pps):
                                   "no NCCL on the data path)",
                    "l2": "inputs and working set exceed the 126 MB L2; no flush needed",
                    "baseline": "BASELINE.md row 15: reference forest W=8 build, 4.2e5 points/s",
-                   "replicas_consistent": consistent,
+                   "replicas_consistent": consistent, "tree_matches_single_gpu": matches,
                    "heap": "torch symmetric memory + NVLS multicast stores for the tree arrays" if db.multicast
                    else ("torch symmetric memory, unicast P2P stores" if db._symm is not None else "cudaMalloc + CUDA IPC, unicast P2P stores"), "host_generate_s": round(gen_s, 2)},
         "clocks": clocks,

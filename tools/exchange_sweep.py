@@ -27,7 +27,11 @@ log2n = int(sys.argv[1]) if len(sys.argv) > 1 else 24
 dim = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 n = 1 << log2n
 first, local = kd.models.slice_bounds(n, world, rank)
-pts = kd.ops.generate_uniform(1, dim, local, first).to(dev)
+dist_name = sys.argv[3] if len(sys.argv) > 3 else "uniform"
+if dist_name == "clustered":   # Gaussian blobs (BASELINE.json config 4): skewed medians, uneven redistribution
+    pts = kd.ops.generate_clustered(1, dim, n)[first:first + local].contiguous().to(dev)
+else:
+    pts = kd.ops.generate_uniform(1, dim, local, first).to(dev)
 b = db.IpcDistBuild(n, dim, with_tree_points=True)
 L = kd.lib()
 st = torch.cuda.current_stream().cuda_stream
@@ -90,7 +94,69 @@ for r in rec:
                  "sync_fixup_ms": round(float(t[2]), 3), "nvlink_bytes_out_per_gpu": out_bytes,
                  "exchange_GBps_per_direction": round(gbs, 1), "frac_of_770_measured": round(gbs / 770, 3),
                  "frac_of_900_nominal": round(gbs / 900, 3)})
+# Load-balance report (SURVEY.md 7.2b, config 4): bytes every rank pushes to every peer per level, from the ranks' own
+# counters (an extra, untimed build that stops after every level to read them).
+def owner_spans(first, count, total, members):
+    """[(member, n)] of the output slots [first, first+count) of a child range of `total` slots spread over `members`."""
+    base, rem, out, o = total // members, total % members, [], first
+    while count > 0:
+        big = rem * (base + 1)
+        mem = o // (base + 1) if o < big else rem + (o - big) // base
+        start = mem * (base + 1) if mem < rem else big + (mem - rem) * base
+        size = base + 1 if mem < rem else base
+        k = min(count, start + size - o)
+        out.append((mem, k))
+        o += k
+        count -= k
+    return out
+
+
+def seg(N, level, s):
+    lo, cnt = 0, N
+    for b in range(level - 1, -1, -1):
+        m = cnt // 2
+        if (s >> b) & 1:
+            lo, cnt = lo + m + 1, cnt - m - 1
+        else:
+            cnt = m
+    return lo, cnt
+
+
+balance = []
+b.serial += 1
+b.load(pts)
+for level in range(levels):
+    for ph, ps in steps:
+        kd._lib.check(L.kd_dist_phase(C.byref(b.ctx), level, ph, ps, b.serial, st), "phase")
+    cnt = (C.c_uint32 * 8)()
+    kd._lib.check(L.kd_dist_level_counts(C.byref(b.ctx), cnt, st), "counts")
+    G = world >> level
+    gb, j = (rank // G) * G, rank % G
+    _, gn = seg(n, level, rank // G)
+    m, nr, Gh = gn // 2, gn - gn // 2 - 1, G // 2
+    local_n, lc, mine, Loff, Roff = cnt[0], cnt[1], cnt[2], cnt[3], cnt[4]
+    free_n = local_n - 1 if j == G - 1 else local_n
+    rc = free_n - lc - mine
+    row = [0] * world
+    for mem, k in owner_spans(Loff, lc, m, Gh):
+        row[gb + mem] += k * 4 * (dim + 1)
+    for mem, k in owner_spans(Roff, rc, nr, Gh):
+        row[gb + Gh + mem] += k * 4 * (dim + 1)
+    allrows = [None] * world
+    dist.all_gather_object(allrows, {"rank": rank, "bytes_to_peer": row, "bracket_used": int(cnt[7]),
+                                     "candidates": int(cnt[6]), "local_points": int(local_n)})
+    if rank == 0:
+        sent = [sum(v for p, v in enumerate(r["bytes_to_peer"]) if p != r["rank"]) for r in allrows]
+        recv = [sum(r["bytes_to_peer"][p] for r in allrows if r["rank"] != p) for p in range(world)]
+        balance.append({"level": level, "ranks": allrows, "max_over_mean_sent": round(max(sent) / (sum(sent) / world), 3),
+                        "max_over_mean_received": round(max(recv) / (sum(recv) / world), 3)})
+kd._lib.check(L.kd_dist_local_build(C.byref(b.ctx), st), "local")
+kd._lib.check(L.kd_dist_done(C.byref(b.ctx), 1, b.serial, st), "done")
+kd._lib.check(L.kd_dist_done(C.byref(b.ctx), 0, b.serial, st), "done")
+torch.cuda.synchronize()
+b.status()
 if rank == 0:
-    print(json.dumps({"n": n, "dim": dim, "world": world, "rows": rows}, indent=1))
+    print(json.dumps({"n": n, "dim": dim, "world": world, "distribution": dist_name, "rows": rows,
+                      "per_peer_bytes_per_level": balance}, indent=1))
 b.close()
 dist.destroy_process_group()
