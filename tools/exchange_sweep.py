@@ -156,6 +156,19 @@ kd._lib.check(L.kd_dist_done(C.byref(b.ctx), 0, b.serial, st), "done")
 torch.cuda.synchronize()
 b.status()
 if rank == 0:
+    # link bytes of a level = what the busiest GPU really pushed to other GPUs (from the counters above), not an estimate
+    for r in rows:
+        if "level" not in r:
+            continue
+        bl = balance[r["level"]]
+        sent = [sum(v for p, v in enumerate(x["bytes_to_peer"]) if p != x["rank"]) for x in bl["ranks"]]
+        recv = [sum(x["bytes_to_peer"][p] for x in bl["ranks"] if x["rank"] != p) for p in range(world)]
+        busiest = max(max(sent), max(recv))
+        gbs = busiest / (r["partition_ms"] * 1e-3) / 1e9
+        r.update({"nvlink_bytes_busiest_gpu": busiest, "nvlink_bytes_mean_per_gpu": int(sum(sent) / world),
+                  "exchange_GBps_per_direction": round(gbs, 1), "frac_of_770_measured": round(gbs / 770, 3),
+                  "frac_of_900_nominal": round(gbs / 900, 3)})
+        r.pop("nvlink_bytes_out_per_gpu", None)
     print(json.dumps({"n": n, "dim": dim, "world": world, "distribution": dist_name, "rows": rows,
                       "per_peer_bytes_per_level": balance}, indent=1))
 b.close()
