@@ -701,8 +701,6 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
     const unsigned Gh = (unsigned)g.G >> 1;              // members per child range
     const unsigned Loff = ctl->Loff, Roff = ctl->Roff;
     const Cols src = cols_of(P, P.rank, cur);
-    Cols dst[kMaxWorld];
-    for (int r = 0; r < g.G; ++r) dst[r] = cols_of(P, g.gb + r, cur ^ 1);
     const unsigned chunk = (free_n + gridDim.x - 1) / gridDim.x;
     const unsigned b = min(blockIdx.x * chunk, free_n), e = min(b + chunk, free_n);
     unsigned long long best = 0ull;
@@ -716,7 +714,7 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
         const unsigned p = local_n - 1u;
         unsigned mem, pos;
         owner_of(nr - 1u, nr, Gh, mem, pos);
-        const Cols& d = dst[Gh + mem];
+        const Cols d = cols_of(P, g.gb + Gh + mem, cur ^ 1);
 #pragma unroll
         for (int c = 0; c < NCOL; ++c) d.c[c][pos] = src.c[c][p];
         d.idx[pos] = src.idx[p];
@@ -796,8 +794,9 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
         }
         __syncthreads();
         // ... and push it out as contiguous runs with 16-byte stores (a run = the part of the left or right
-        // output that lands on one owner GPU; there are at most a few per tile): a warp then emits 512
-        // contiguous bytes per store instruction, which is what the NVLink egress path wants
+        // output that lands on one owner GPU; there are at most a few per tile).  Every warp takes whole columns
+        // (warp w: columns w, w + warps, ...; the index column counts as one), so all columns stream at once and
+        // a warp emits 512 contiguous bytes per store instruction, which is what the NVLink egress path wants.
         for (int side_i = 0; side_i < 2; ++side_i) {
             const unsigned cnt = side_i ? nrt : nl, s_first = side_i ? nl : 0u;
             const unsigned n_c = side_i ? nr : m;
@@ -808,22 +807,21 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
                 owner_of(o, n_c, Gh, mem, pos);
                 const unsigned room = share_of(n_c, Gh, mem) - pos;   // slots left on this owner
                 const unsigned k = min(cnt - done, room);
-                const Cols& d = dst[side_i ? Gh + mem : mem];
+                unsigned char* dheap = P.heap[g.gb + (side_i ? Gh + mem : mem)];
                 const unsigned s0 = s_first + done;
                 const unsigned head = min(k, (4u - (pos & 3u)) & 3u);  // elements before the first 16-byte boundary
                 const unsigned body = (k - head) >> 2;                 // whole 16-byte chunks
                 const unsigned tail0 = head + (body << 2);
-#pragma unroll
-                for (int c = 0; c <= NCOL; ++c) {
+                for (int c = tid >> 5; c <= NCOL; c += BLOCK / 32) {
                     const float* __restrict__ sc = c < NCOL ? stage + (size_t)c * (BLOCK * IPT) + s0
                                                            : reinterpret_cast<const float*>(stage_idx) + s0;
-                    float* __restrict__ dc = (c < NCOL ? d.c[c < NCOL ? c : 0] : reinterpret_cast<float*>(d.idx)) + pos;
-                    if ((unsigned)tid < head) dc[tid] = sc[tid];
-                    for (unsigned q = tid; q < body; q += BLOCK) {
+                    float* __restrict__ dc = reinterpret_cast<float*>(dheap + (c < NCOL ? P.L.col[cur ^ 1][c] : P.L.idx[cur ^ 1])) + pos;
+                    if ((unsigned)lane < head) dc[lane] = sc[lane];
+                    for (unsigned q = lane; q < body; q += 32) {
                         const unsigned e0 = head + (q << 2);
                         *reinterpret_cast<float4*>(dc + e0) = make_float4(sc[e0], sc[e0 + 1], sc[e0 + 2], sc[e0 + 3]);
                     }
-                    if (tail0 + tid < k) dc[tail0 + tid] = sc[tail0 + tid];
+                    if (tail0 + lane < k) dc[tail0 + lane] = sc[tail0 + lane];
                 }
                 done += k;
             }
