@@ -26,6 +26,11 @@ extern "C" {
 
 const char* kd_last_error(void);
 int kd_version(void);
+/* -DKD_DEBUG builds of the library (libkdtree_b200_dbg.so) check every computed store offset of the build kernels on
+ * the device; kd_debug_bounds_status() synchronises the device and fails with the code of the first assertion that
+ * failed since the last call.  Release builds: kd_debug_enabled() == 0 and the status is always 0. */
+int kd_debug_enabled(void);
+int kd_debug_bounds_status(void);
 void kd_free(void* p); /* releases buffers returned by the kd_format_* functions */
 
 /* ---- problem generation (reference Utility.cpp:6-18, kdtree_mpi.cpp:19-41) ---- */

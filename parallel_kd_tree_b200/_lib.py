@@ -49,6 +49,8 @@ def _declare(lib):
         "kd_format_head_and_leaves": (i32, [vp, i64, i32, vp, i32, C.POINTER(vp), C.POINTER(C.c_size_t)]),
         "kd_build_workspace_bytes": (C.c_size_t, [i64, i32]),
         "kd_build_gpu": (i32, [vp, i64, i32, vp, vp, vp, C.c_size_t, vp]),
+        "kd_debug_enabled": (i32, []),
+        "kd_debug_bounds_status": (i32, []),
         "kd_build_gpu_noalloc": (i32, [vp, i64, i32, vp, vp, vp]),
         "kd_build_status_noalloc": (i32, [i64, i32, vp]),
         "kd_build_status": (i32, [vp, i64, i32, vp]),
@@ -95,9 +97,10 @@ def lib():
     if _lib is None:
         with _lock:
             if _lib is None:
-                path = _build.LIB
+                debug = os.environ.get("KD_B200_DEBUG") == "1"     # the -DKD_DEBUG variant (bounds assertions)
+                path = _build.LIB_DBG if debug else _build.LIB
                 if os.environ.get("KD_B200_NO_BUILD") != "1":
-                    path = _build.build_library()
+                    path = _build.build_library(debug=debug)
                 elif not path.exists():
                     raise KdError(f"{path} is missing and KD_B200_NO_BUILD=1 forbids building it")
                 handle = C.CDLL(str(path))

@@ -20,6 +20,7 @@ PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 OUT_DIR = PKG / "_C"
 LIB = OUT_DIR / "libkdtree_b200.so"
+LIB_DBG = OUT_DIR / "dbg" / "libkdtree_b200_dbg.so"
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -50,26 +51,32 @@ def _stamp() -> str:
     return h.hexdigest()
 
 
-def needs_build() -> bool:
-    stamp = OUT_DIR / "build.stamp"
-    return not (LIB.exists() and stamp.exists() and stamp.read_text() == _stamp())
+def needs_build(debug: bool = False) -> bool:
+    lib, out = (LIB_DBG, OUT_DIR / "dbg") if debug else (LIB, OUT_DIR)
+    stamp = out / "build.stamp"
+    return not (lib.exists() and stamp.exists() and stamp.read_text() == _stamp())
 
 
-def build_library(force: bool = False, verbose: bool = False) -> Path:
-    """Compile every source under csrc/ for sm_100a and link the shared library."""
-    if not force and not needs_build():
-        return LIB
-    OUT_DIR.mkdir(exist_ok=True)
+def build_library(force: bool = False, verbose: bool = False, debug: bool = False) -> Path:
+    """Compile every source under csrc/ for sm_100a and link the shared library.
+
+    ``debug``: the -DKD_DEBUG variant (``libkdtree_b200_dbg.so``, objects under ``_C/dbg``): same kernels with a
+    bounds assertion on every computed store offset (kd_common.h); ``KD_B200_DEBUG=1`` makes the package load it."""
+    lib, out_dir = (LIB_DBG, OUT_DIR / "dbg") if debug else (LIB, OUT_DIR)
+    if not force and not needs_build(debug):
+        return lib
+    out_dir.mkdir(parents=True, exist_ok=True)
     nvcc = _nvcc()
     srcs = sources()
-    log_dir = OUT_DIR / "log"
+    log_dir = out_dir / "log"
     log_dir.mkdir(exist_ok=True)
+    flags = NVCC_FLAGS + (["-DKD_DEBUG"] if debug else [])
 
     def compile_one(src: Path) -> Path:
-        obj = OUT_DIR / (src.stem + ".o")
-        cmd = [nvcc, *NVCC_FLAGS, "-c", str(src), "-o", str(obj)]
+        obj = out_dir / (src.stem + ".o")
+        cmd = [nvcc, *flags, "-c", str(src), "-o", str(obj)]
         if src.suffix == ".cpp":
-            cmd = [nvcc, *NVCC_FLAGS, "-x", "cu", "-c", str(src), "-o", str(obj)]
+            cmd = [nvcc, *flags, "-x", "cu", "-c", str(src), "-o", str(obj)]
         r = subprocess.run(cmd, capture_output=True, text=True)
         (log_dir / (src.stem + ".ptxas.txt")).write_text(r.stdout + r.stderr)
         if r.returncode != 0:
@@ -80,16 +87,16 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
 
     with cf.ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
         objs = list(ex.map(compile_one, srcs))
-    tmp = OUT_DIR / "libkdtree_b200.so.tmp"
+    tmp = out_dir / (lib.name + ".tmp")
     r = subprocess.run(
         [nvcc, "-shared", "-o", str(tmp), *map(str, objs), "-cudart", "static", "-lpthread"],
         capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
-    os.replace(tmp, LIB)
-    (OUT_DIR / "build.stamp").write_text(_stamp())
-    return LIB
+    os.replace(tmp, lib)
+    (out_dir / "build.stamp").write_text(_stamp())
+    return lib
 
 
 if __name__ == "__main__":
-    print(build_library(force="--force" in sys.argv, verbose=True))
+    print(build_library(force="--force" in sys.argv, verbose=True, debug="--debug" in sys.argv))

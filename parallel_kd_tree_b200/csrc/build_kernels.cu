@@ -204,8 +204,10 @@ __global__ void __launch_bounds__(BLOCK) k_bracket(const float* __restrict__ key
 #pragma unroll
         for (int k = 0; k < IPT; ++k)
             if (cmask & (1u << k)) {
-                cand_key[p] = f[k];
-                cand_idx[p] = (int32_t)(tb + k * BLOCK + tid);  // the candidate's slot; its index is fetched on demand
+                if (KD_INB(p >= b && p < e, 903)) {   // a chunk's candidates can never outgrow the chunk
+                    cand_key[p] = f[k];
+                    cand_idx[p] = (int32_t)(tb + k * BLOCK + tid);  // the candidate's slot; its index is fetched on demand
+                }
                 ++p;
             }
     }
@@ -482,6 +484,8 @@ __global__ void __launch_bounds__(BLOCK) k_partition(Cols src, Cols dst, const f
                 continue;
             }
             unsigned p = (side[k] == -1 ? baseL : baseR) + rk[k];
+            // left elements fill [lo, lo+m), right ones [lo+m+1, lo+n-1) (the last slot belongs to the pinned element)
+            if (!KD_INB(side[k] == -1 ? (p >= lo && p < lo + m) : (p > lo + m && p < lo + n - 1u), 901)) continue;
 #pragma unroll
             for (int c = 0; c < NCOL; ++c) dst.c[c][p] = val[k][c];
             dst.idx[p] = id[k];
@@ -542,6 +546,7 @@ __global__ void __launch_bounds__(256) k_fixup(Cols dst, int ncol, const MaxRec*
     seg_range(N, level, s, lo, n);
     unsigned last = lo + (n >> 1) - 1;
     if (bestpos == last) return;
+    if (!KD_INB(bestpos >= lo && bestpos < last, 904)) return;
     if (lane < ncol) {
         float a = dst.c[lane][bestpos], b = dst.c[lane][last];
         dst.c[lane][bestpos] = b;
@@ -730,6 +735,7 @@ __global__ void __launch_bounds__(512, (NCOL <= 4 ? 3 : 1)) k_medium(Cols src, C
                 continue;
             }
             const unsigned p = side == -1 ? lo + wl + __popc(bl & lt) : lo + m + 1 + wr + __popc(br & lt);
+            if (!KD_INB(side == -1 ? p < lo + m : (p > lo + m && p < lo + n - 1u), 902)) continue;
 #pragma unroll
             for (int c = 0; c < NCOL; ++c) dst.c[c][p] = val[u][c];
             dst.idx[p] = id[u];
@@ -1045,7 +1051,7 @@ __device__ __forceinline__ void sub_team_level(const SubCtx& C, int j, int logP,
         for (int e = 0; e < 8; ++e) {
             const bool a = (alive >> e) & 1u;
             const unsigned b = __ballot_sync(FULL, a) & tmask;
-            if (a) L[run + __popc(b & lt)] = comp[e];
+            if (a && KD_INB(run + __popc(b & lt) < (kCta ? kSubListPerWarp : kSubListPerWarp / tpw), 907)) L[run + __popc(b & lt)] = comp[e];
             run += __popc(b);
         }
         if (active && tl == 0 && r == 0u) XM[1] = 0ull;
@@ -1118,7 +1124,7 @@ __device__ __forceinline__ void sub_team_level(const SubCtx& C, int j, int logP,
             unsigned pos;
             if ((lessX >> e) & 1u) pos = ((isM >> e) & 1u) ? m - 1u : exL++;
             else pos = ((isX >> e) & 1u) ? m : exR++;
-            C.sord[slo + pos] = (unsigned short)slot[e];
+            if (KD_INB(pos + 1u < sn && slo + pos < (unsigned)kFinishT, 905)) C.sord[slo + pos] = (unsigned short)slot[e];
         }
     if (in_range && tl == 0) {
         tabn[(2u * q) << (logP - 3)] = (slo << 16) | m;
@@ -1181,7 +1187,7 @@ __device__ __forceinline__ void sub_thread_level(const SubCtx& C, int j, int axi
             }
 #pragma unroll
     for (int e = 0; e < 8; ++e)
-        if (comp[e] != ~0ull) C.sord[glo[e >> LOGP] + rank[e]] = (unsigned short)slot[e];
+        if (comp[e] != ~0ull && KD_INB(rank[e] + 1u < gn[e >> LOGP], 906)) C.sord[glo[e >> LOGP] + rank[e]] = (unsigned short)slot[e];
     __syncwarp();
 }
 
@@ -1543,6 +1549,28 @@ int kd_build_status(const void* workspace, int64_t n, int dim, void* stream) {
     if (e == cudaSuccess) e = cudaStreamSynchronize((cudaStream_t)stream);
     if (e != cudaSuccess) return kd::fail(std::string("kd_build_status: ") + cudaGetErrorString(e));
     if (err) return kd::fail("kd_build_gpu: select lost its rank in digit pass " + std::to_string(err - 1));
+    return 0;
+}
+
+/* -DKD_DEBUG builds: device-side bounds assertions (see kd_common.h).  Returns 0 if none failed since the last call
+ * (and in release builds, where kd_debug_enabled() is 0), else fails with the code of the first one. */
+int kd_debug_enabled(void) {
+#if defined(KD_DEBUG)
+    return 1;
+#else
+    return 0;
+#endif
+}
+int kd_dist_debug_err(void);
+int kd_debug_bounds_status(void) {
+#if defined(KD_DEBUG)
+    int a = 0, zero = 0;
+    if (cudaDeviceSynchronize() != cudaSuccess || cudaMemcpyFromSymbol(&a, kd_dbg_err, sizeof(int)) != cudaSuccess ||
+        cudaMemcpyToSymbol(kd_dbg_err, &zero, sizeof(int)) != cudaSuccess)
+        return kd::fail("kd_debug_bounds_status: could not read the assertion word");
+    const int b = kd_dist_debug_err();
+    if (a || b) return kd::fail("bounds assertion failed on the device, code " + std::to_string(a ? a : b));
+#endif
     return 0;
 }
 

@@ -812,6 +812,8 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
                 const unsigned head = min(k, (4u - (pos & 3u)) & 3u);  // elements before the first 16-byte boundary
                 const unsigned body = (k - head) >> 2;                 // whole 16-byte chunks
                 const unsigned tail0 = head + (body << 2);
+                // the run [pos, pos + k) must lie inside the owner's share of the child range and inside its columns
+                if (!KD_INB(mem < Gh && pos + k <= share_of(n_c, Gh, mem) && (size_t)pos + k <= (size_t)P.L.cap, 951)) { done += k; continue; }
                 for (int c = tid >> 5; c <= NCOL; c += BLOCK / 32) {
                     const float* __restrict__ sc = c < NCOL ? stage + (size_t)c * (BLOCK * IPT) + s0
                                                            : reinterpret_cast<const float*>(stage_idx) + s0;
@@ -1429,6 +1431,18 @@ int kd_dist_level_counts(const kd_dist_ctx* ctx, uint32_t* out, void* stream) {
     out[0] = c.cnt; out[1] = c.my_less; out[2] = c.mine; out[3] = c.Loff; out[4] = c.Roff;
     out[5] = c.cL; out[6] = c.cand_cnt; out[7] = (uint32_t)c.use_cand;
     return 0;
+}
+
+/* first failed bounds assertion of the distributed kernels (-DKD_DEBUG builds; 0 otherwise); clears it */
+int kd_dist_debug_err(void) {
+#if defined(KD_DEBUG)
+    int a = 0, zero = 0;
+    if (cudaMemcpyFromSymbol(&a, kd_dbg_err, sizeof(int)) != cudaSuccess) return -1;
+    cudaMemcpyToSymbol(kd_dbg_err, &zero, sizeof(int));
+    return a;
+#else
+    return 0;
+#endif
 }
 
 /* the (phase, pass) pairs of one distributed level in launch order; returns their number (<= cap) */

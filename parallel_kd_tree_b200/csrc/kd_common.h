@@ -59,3 +59,14 @@ KD_HD int digit_bits(int d) { return (d == 2 || d == 5) ? 10 : 11; }
 KD_HD int select_digit_shift(int hi) { return hi > 32 ? (hi - 11 > 32 ? hi - 11 : 32) : (hi - 11 > 0 ? hi - 11 : 0); }
 
 }  // namespace kd
+
+// Sanitizer substitute (compute-sanitizer is closed on the development pool): a -DKD_DEBUG build checks every computed
+// store offset of the build kernels against the range it must fall into.  A failed check records its code (first one
+// wins), SKIPS the store and lets the kernel run on, so barriers stay balanced; kd_debug_bounds_status() reports it.
+// In release builds KD_INB(cond, code) is the constant `true` and costs nothing.
+#if defined(KD_DEBUG) && defined(__CUDACC__)
+static __device__ int kd_dbg_err;   // one per translation unit
+#define KD_INB(cond, code) ((cond) ? true : (atomicCAS(&kd_dbg_err, 0, (code)), false))
+#else
+#define KD_INB(cond, code) true
+#endif

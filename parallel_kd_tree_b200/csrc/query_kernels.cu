@@ -225,16 +225,30 @@ __global__ void k_bbox_init(unsigned* mn, unsigned* mx, int dim) {
 
 __global__ void __launch_bounds__(256) k_bbox(const float* __restrict__ pts, size_t total, int dim, size_t stride,
                                               unsigned* mn, unsigned* mx) {
-    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= stride) return;
+    // per-thread running min / max, then ONE shared-memory atomic pair per thread and one global atomic pair per
+    // CTA and axis (round 1 issued a global atomic pair per thread)
+    __shared__ unsigned s_mn[256], s_mx[256];
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool small = dim <= 256;
+    if (small) { s_mn[threadIdx.x] = 0xffffffffu; s_mx[threadIdx.x] = 0u; }
+    __syncthreads();
     unsigned lo = 0xffffffffu, hi = 0u;
-    for (size_t e = t; e < total; e += stride) {
-        unsigned k = ordered_key(pts[e]);
-        lo = min(lo, k);
-        hi = max(hi, k);
+    if (t < stride)
+        for (size_t e = t; e < total; e += stride) {
+            const unsigned k = ordered_key(pts[e]);
+            lo = min(lo, k);
+            hi = max(hi, k);
+        }
+    const int axis = (int)(t % (size_t)dim);
+    if (lo <= hi) {
+        if (small) { atomicMin(&s_mn[axis], lo); atomicMax(&s_mx[axis], hi); }
+        else { atomicMin(&mn[axis], lo); atomicMax(&mx[axis], hi); }
     }
-    int axis = (int)(t % (size_t)dim);
-    if (lo <= hi) { atomicMin(&mn[axis], lo); atomicMax(&mx[axis], hi); }
+    __syncthreads();
+    if (small && (int)threadIdx.x < dim && s_mn[threadIdx.x] <= s_mx[threadIdx.x]) {
+        atomicMin(&mn[threadIdx.x], s_mn[threadIdx.x]);
+        atomicMax(&mx[threadIdx.x], s_mx[threadIdx.x]);
+    }
 }
 
 __global__ void k_bbox_finish(unsigned* mn, unsigned* mx, int dim) {
