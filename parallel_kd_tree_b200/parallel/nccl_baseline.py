@@ -5,8 +5,9 @@ The same tree as the product builds, produced the conventional way:
 * distributed levels: radix select whose histograms are summed with ``all_reduce``, points moved with
   ``all_to_all_single``, result gathered with ``all_gather_into_tensor`` — one collective call per step,
   nothing fused;
-* every level below: one ``torch.sort`` over the whole local array, keyed by (unit, key) with a stable
-  pre-sort on the point index.  A *unit* is what must stay together: the unpinned part of a range, a
+* every level below: library sorts over the whole local array, keyed by (unit, key) with a stable pre-sort on
+  the point index (two ``torch.sort`` calls per level: (segment, key, index) is 88 bits wide and ``torch.sort``
+  takes one 64-bit key; no host synchronisation inside the level loop).  A *unit* is what must stay together: the unpinned part of a range, a
   range's pinned last element, or an already placed node; units are numbered by position, so one global
   sort per level sorts every range's first n-1 elements in place (exactly kdtree_sequential.cpp:46-48).
 
@@ -62,7 +63,7 @@ def sort_build_local(pts: torch.Tensor, idx: torch.Tensor, depth0: int) -> torch
     cnt = torch.full((n,), n, dtype=torch.int64, device=dev)  # and size; 0 = the slot holds a placed node
     pos = torch.arange(n, device=dev)
     level = 0
-    while int(cnt.max()) >= 3:
+    while (n >> level) >= 3:      # the left-most range is the largest; its size depends on n only (no device read-back)
         axis = (depth0 + level) % dim
         free = (cnt > 0) & (pos < lo + cnt - 1)
         unit = torch.where(free, lo, pos)                    # pinned elements and nodes are their own unit
