@@ -244,11 +244,10 @@ __global__ void k_bracket_finish(SegState* st, unsigned N, int level, unsigned n
 
 template <int BLOCK, int UNROLL>
 __global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys_all, const int32_t* __restrict__ idx_all,
-                                                const float* __restrict__ cand_key,
-                                                const int32_t* __restrict__ cand_idx,
-                                                const unsigned* __restrict__ cand_cta, SegState* st,
+                                                float* cand_key, int32_t* cand_idx, unsigned* cand_cta, SegState* st,
                                                 unsigned* __restrict__ ghist, unsigned N, int level, int cps, int d) {
     __shared__ unsigned sh[kDigitBins];
+    __shared__ unsigned s_w;   // survivors re-compacted by this CTA (see below)
     unsigned s = blockIdx.x / cps, j = blockIdx.x % cps;
     SegState S = st[s];
     if (S.done == 1) return;
@@ -256,7 +255,7 @@ __global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys_a
     seg_range(N, level, s, lo, n);
     // the pinned last slot never takes part (kdtree_sequential.cpp:46-48); after a successful bracket the
     // passes run on the range's candidates instead of on all of its keys
-    const float* __restrict__ keys = S.use_cand ? cand_key : keys_all;
+    const float* keys = S.use_cand ? cand_key : keys_all;
     const bool via = S.use_cand != 0;  // candidates carry their slot; the point index is read through it
     auto point_index = [&](unsigned i) -> unsigned { return (unsigned)(via ? idx_all[cand_idx[i]] : idx_all[i]); };
     const unsigned free_n = n - 1;
@@ -285,6 +284,7 @@ __global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys_a
         return;
     }
     for (int t = threadIdx.x; t < kDigitBins; t += BLOCK) sh[t] = 0;
+    if (threadIdx.x == 0) s_w = 0;
     __syncthreads();
     // bits [hi, 64) of the composite are resolved; this pass counts the digit right below them (at most 11 bits,
     // never straddling the key | index boundary)
@@ -292,6 +292,11 @@ __global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys_a
     const unsigned mask = (1u << (hi - dsh)) - 1u;
     const unsigned iters = (e - b + BLOCK * UNROLL - 1) / (BLOCK * UNROLL);
     (void)d;
+    // Once a digit has been chosen only a sliver of the candidates still matches the prefix (1 / 2048 after the
+    // first digit), yet every later pass would stream all of them again.  So a pass that sees few matches re-compacts
+    // them, in place, to the front of this CTA's own run (the writes of a tile land below the next tile's reads) and
+    // shortens the run: the following passes and the read-back touch the survivors only.
+    const bool compact = via && S.cnt * 8u < S.cand_cnt;
     if (hi > 32) {
         const int ks = dsh - 32, ps = hi - 32;
         const unsigned want = hi >= 64 ? 0u : (unsigned)(S.prefix >> hi);
@@ -300,12 +305,27 @@ __global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys_a
             float f[UNROLL];
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u) f[u] = (i0 + u * BLOCK) < e ? keys[i0 + u * BLOCK] : 0.f;
+            unsigned vm = 0u;
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u) {
                 bool valid = (i0 + u * BLOCK) < e;
                 unsigned key = ordered_key(f[u]);
                 if (hi < 64) valid = valid && ((key >> ps) == want);
                 warp_hist_add(sh, (key >> ks) & mask, valid);
+                vm |= valid ? (1u << u) : 0u;
+            }
+            if (compact) {
+                int32_t slot[UNROLL];
+#pragma unroll
+                for (int u = 0; u < UNROLL; ++u) slot[u] = ((vm >> u) & 1u) ? cand_idx[i0 + u * BLOCK] : 0;
+                __syncthreads();   // every read of this tile is done before its range may be overwritten
+#pragma unroll
+                for (int u = 0; u < UNROLL; ++u)
+                    if ((vm >> u) & 1u) {
+                        const unsigned p = b + atomicAdd(&s_w, 1u);
+                        cand_key[p] = f[u];
+                        cand_idx[p] = slot[u];
+                    }
             }
         }
     } else {
@@ -316,17 +336,32 @@ __global__ void __launch_bounds__(BLOCK) k_hist(const float* __restrict__ keys_a
             float f[UNROLL];
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u) f[u] = (i0 + u * BLOCK) < e ? keys[i0 + u * BLOCK] : 0.f;
+            unsigned vm = 0u;
+            int32_t slot[UNROLL];
 #pragma unroll
             for (int u = 0; u < UNROLL; ++u) {
                 unsigned i = i0 + u * BLOCK;
                 bool valid = i < e && ordered_key(f[u]) == wantkey;
-                unsigned id = valid ? point_index(i) : 0u;
+                slot[u] = (valid && via) ? cand_idx[i] : (int32_t)i;
+                unsigned id = valid ? (unsigned)idx_all[slot[u]] : 0u;
                 if (hi < 32) valid = valid && ((id >> hi) == wantidx);
                 warp_hist_add(sh, (id >> dsh) & mask, valid);
+                vm |= valid ? (1u << u) : 0u;
+            }
+            if (compact) {
+                __syncthreads();
+#pragma unroll
+                for (int u = 0; u < UNROLL; ++u)
+                    if ((vm >> u) & 1u) {
+                        const unsigned p = b + atomicAdd(&s_w, 1u);
+                        cand_key[p] = f[u];
+                        cand_idx[p] = slot[u];
+                    }
             }
         }
     }
     __syncthreads();
+    if (compact && threadIdx.x == 0) cand_cta[blockIdx.x] = s_w;
     unsigned* gh = ghist + (size_t)s * kDigitBins;
     for (int t = threadIdx.x; t < kDigitBins; t += BLOCK) {
         unsigned v = sh[t];
