@@ -107,34 +107,38 @@ __device__ __forceinline__ void warp_hist_add(unsigned* sh, unsigned digit, bool
 // candidate arrays (k_bracket); the digit passes then run on the candidates only.  The result is exact: the
 // counts prove whether the wanted rank is inside the bracket, and if it is not (or for adversarial orderings
 // of the input) the range simply falls back to digit passes over all of its keys.
-constexpr int kSampleN = 1024;   // sample size per range
-constexpr int kSampleDelta = 72; // half-width of the bracket in sample ranks (4.5 sigma of a random sample's rank)
-
+// Sample size per range: 1024, or 4096 for ranges of at least 2^20 points, where halving the bracket (14 % -> 7 % of
+// the range) saves more in the candidate passes than the larger sort costs.  The half-width of the bracket is 4.5
+// sigma of a random sample's rank (sigma = sqrt(S) / 2): 72 of 1024, 144 of 4096.
+template <int SN>
 __global__ void __launch_bounds__(512) k_sample(const float* __restrict__ keys, const int32_t* __restrict__ idx,
                                                 SegState* st, unsigned N, int level) {
-    __shared__ unsigned long long sm[kSampleN];
+    constexpr int kDelta = SN == 1024 ? 72 : 144;
+    __shared__ unsigned long long sm[SN];
     unsigned lo, n;
     seg_range(N, level, blockIdx.x, lo, n);
     const unsigned free_n = n - 1, m = n >> 1, tid = threadIdx.x;
-    for (unsigned k = tid; k < (unsigned)kSampleN; k += 512) {
-        const unsigned pos = lo + (unsigned)(((unsigned long long)k * free_n) / kSampleN);  // systematic sample
+    for (unsigned k = tid; k < (unsigned)SN; k += 512) {
+        const unsigned pos = lo + (unsigned)(((unsigned long long)k * free_n) / SN);  // systematic sample
         sm[k] = composite(ordered_key(keys[pos]), (unsigned)idx[pos]);
     }
     __syncthreads();
-    for (unsigned k = 2; k <= (unsigned)kSampleN; k <<= 1) {
+    for (unsigned k = 2; k <= (unsigned)SN; k <<= 1) {
         for (unsigned j = k >> 1; j > 0; j >>= 1) {
-            const unsigned i = ((tid & ~(j - 1u)) << 1) | (tid & (j - 1u)), l = i | j;  // tid-th pair at distance j
-            const bool asc = (i & k) == 0u;
-            const unsigned long long a = sm[i], b = sm[l];
-            if ((a > b) == asc) { sm[i] = b; sm[l] = a; }
+            for (unsigned t = tid; t < (unsigned)SN / 2; t += 512) {
+                const unsigned i = ((t & ~(j - 1u)) << 1) | (t & (j - 1u)), l = i | j;  // t-th pair at distance j
+                const bool asc = (i & k) == 0u;
+                const unsigned long long a = sm[i], b = sm[l];
+                if ((a > b) == asc) { sm[i] = b; sm[l] = a; }
+            }
             __syncthreads();
         }
     }
     if (tid == 0) {
-        const int r = (int)(((unsigned long long)m * kSampleN) / free_n);
-        const int li = r - kSampleDelta, hi = r + kSampleDelta;
+        const int r = (int)(((unsigned long long)m * SN) / free_n);
+        const int li = r - kDelta, hi = r + kDelta;
         st[blockIdx.x].lowP = li < 0 ? 0ull : sm[li];
-        st[blockIdx.x].highP = hi >= kSampleN ? ~0ull : sm[hi];
+        st[blockIdx.x].highP = hi >= SN ? ~0ull : sm[hi];
     }
 }
 
@@ -1467,7 +1471,8 @@ int build_core(Cols buf[2], int cur, int64_t n, int dim, int ncol, int depth0, u
         }
         const bool bracket = sc.cand_key != nullptr;
         if (bracket) {
-            k_sample<<<(unsigned)nseg, 512, 0, stream>>>(keys, buf[cur].idx, sc.st, N, level);
+            if (seg_n >= (1ll << 20)) k_sample<4096><<<(unsigned)nseg, 512, 0, stream>>>(keys, buf[cur].idx, sc.st, N, level);
+            else k_sample<1024><<<(unsigned)nseg, 512, 0, stream>>>(keys, buf[cur].idx, sc.st, N, level);
             KD_LAUNCH_CHECK("k_sample");
             k_bracket<512, 8><<<(unsigned)(nseg * cps_p), 512, 0, stream>>>(keys, buf[cur].idx, sc.st, sc.cand_key,
                                                                            sc.cand_idx, sc.cand_cta, N, level, cps_p);
