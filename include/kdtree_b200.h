@@ -134,8 +134,9 @@ int kd_bbox_gpu(const float* points, int64_t n, int dim, float* out_min, float* 
  * kdtree_sequential.cpp:30-66; the reference's own multi-rank program only builds W local trees) ----
  * Every rank owns a "symmetric heap" of kd_dist_heap_bytes() bytes with the same layout; heap[r] is rank r's
  * heap as addressable from the calling rank (CUDA IPC mapping, or plain pointers for W virtual ranks on one GPU).
- * The tree arrays live inside the heap at the offsets reported by kd_dist_offsets().  world must be 1, 2, 4 or 8,
- * dim <= 8. */
+ * The tree arrays live inside the heap at the offsets reported by kd_dist_offsets().  world must be 1, 2, 4 or 8.
+ * dim <= 8: the coordinates travel with the points; larger dim (the reference's default is 128): every rank receives all
+ * points once and only indices move (the heap then holds n_total x dim floats per rank). */
 typedef struct {
     int world, rank, dim, with_tree_points;
     int64_t n_total;
@@ -158,6 +159,8 @@ int kd_dist_schedule(int* phases, int* passes, int cap);
 int kd_dist_level_counts(const kd_dist_ctx* ctx, uint32_t* out, void* stream);
 int kd_dist_local_build(const kd_dist_ctx* ctx, void* stream);
 int kd_dist_done(const kd_dist_ctx* ctx, int post, uint64_t serial, void* stream);
+/* last step after the done-barrier (gather mode, dim > 8: tree_points from the full point array; otherwise nothing) */
+int kd_dist_finish(const kd_dist_ctx* ctx, void* stream);
 /* synchronises the stream; non-zero if a device-side check or a peer wait failed */
 int kd_dist_status(const kd_dist_ctx* ctx, void* stream);
 

@@ -72,6 +72,7 @@ def _declare(lib):
         "kd_dist_run": (i32, [C.POINTER(DistCtx), C.c_uint64, vp]),
         "kd_dist_phase": (i32, [C.POINTER(DistCtx), i32, i32, i32, C.c_uint64, vp]),
         "kd_dist_level_counts": (i32, [C.POINTER(DistCtx), C.POINTER(C.c_uint32), vp]),
+        "kd_dist_finish": (i32, [C.POINTER(DistCtx), vp]),
         "kd_dist_schedule": (i32, [C.POINTER(C.c_int), C.POINTER(C.c_int), i32]),
         "kd_dist_local_build": (i32, [C.POINTER(DistCtx), vp]),
         "kd_dist_done": (i32, [C.POINTER(DistCtx), i32, C.c_uint64, vp]),

@@ -40,7 +40,7 @@
 namespace kd {
 
 constexpr int kMaxWorld = 8;
-enum FlagKind { F_HIST = 0, F_CNT, F_PART, F_MAX, F_FIX, F_DONE, F_SAMP, F_BRK, kNumFlagKinds };
+enum FlagKind { F_HIST = 0, F_CNT, F_PART, F_MAX, F_FIX, F_DONE, F_SAMP, F_BRK, F_ROWS, kNumFlagKinds };
 constexpr int kDSample = 1024;          // sample composites per rank per distributed level
 constexpr int kRedStride = kDigitBins + 32;   // one NVLS accumulator: the bins + its arrival counter (+ padding)
 constexpr int kRedPasses = 8;
@@ -71,6 +71,7 @@ struct DistLayout {
     size_t ctl, flags, hist_slots, lhist, own_hist, samp_slots, brk_slots, racc, cnt_slots, max_slots, rec, col[2][kMaxCarry],
         idx[2], perm, tp;
     size_t st, ghist, lrec, lerr, ckey, cidx, ccta;  // scratch of the local (single-GPU) phase
+    size_t pts_all, keybuf;                          // dim > kMaxCarry: all points on every rank, split-axis keys per level
     size_t bytes;
     int64_t cap, max_seg, max_rec;
 };
@@ -92,10 +93,16 @@ static DistLayout make_layout(int64_t n_total, int dim, int world, bool with_tp)
     L.cnt_slots = take((size_t)kMaxWorld * 4 * 4);
     L.max_slots = take(sizeof(MaxSlot) * kMaxWorld);
     L.rec = take(sizeof(MaxRec) * (size_t)(kTargetCtas + 8));
+    // dim <= kMaxCarry: the coordinates travel with the points in SoA columns.  Larger dim (the reference's default
+    // is 128, Utility.cpp:98): every rank receives ALL points once (the ranks' slices are pushed to every peer before
+    // level 0), only the index column moves afterwards and the split-axis key is gathered per level.
+    const int ncol = dim <= kMaxCarry ? dim : 0;
     for (int b = 0; b < 2; ++b) {
-        for (int c = 0; c < dim; ++c) L.col[b][c] = take((size_t)L.cap * 4);
+        for (int c = 0; c < ncol; ++c) L.col[b][c] = take((size_t)L.cap * 4);
         L.idx[b] = take((size_t)L.cap * 4);
     }
+    L.pts_all = ncol ? 0 : take((size_t)n_total * dim * 4);
+    L.keybuf = ncol ? 0 : take((size_t)L.cap * 4);
     L.perm = take((size_t)n_total * 4);
     L.tp = with_tp ? take((size_t)n_total * dim * 4) : 0;
     int lv = 0;
@@ -235,6 +242,41 @@ __global__ void __launch_bounds__(kDInitBlock) k_dist_init(DistParams P, const f
         for (unsigned r = tid; r < rows; r += kDInitBlock) dst.c[c][row0 + r] = tile[r * P.dim + c];
 }
 
+// gather mode (dim > kMaxCarry): the rank's rows go to its OWN copy of the full point array, indices to column 0
+__global__ void __launch_bounds__(256) k_dist_init_rows(DistParams P, const float* __restrict__ pts, unsigned local_n,
+                                                        unsigned first_row) {
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
+    if (tid == 0) {
+        DistCtl* c = DCTL(P, P.rank);
+        c->cnt = local_n;
+        c->err = 0;
+        c->ticket = 0;
+    }
+    int32_t* idx = reinterpret_cast<int32_t*>(P.heap[P.rank] + P.L.idx[0]);
+    float* all = reinterpret_cast<float*>(P.heap[P.rank] + P.L.pts_all) + (size_t)first_row * P.dim;
+    for (size_t i = tid; i < local_n; i += nth) idx[i] = (int32_t)(first_row + i);
+    const size_t total = (size_t)local_n * P.dim;
+    for (size_t e = tid; e < total; e += nth) all[e] = pts[e];
+}
+
+// split-axis keys of the rank's current elements (gather mode): keybuf[i] = points[idx[i]][axis]
+__global__ void __launch_bounds__(256) k_dist_gather_keys(DistParams P, LevelGeo g, int cur, int axis) {
+    DistCtl* ctl = DCTL(P, P.rank);
+    if (ctl->err) return;
+    const unsigned local_n = g.level > 0 ? share_of(g.n, (unsigned)g.G, (unsigned)g.j) : ctl->cnt;
+    const int32_t* __restrict__ idx = reinterpret_cast<const int32_t*>(P.heap[P.rank] + P.L.idx[cur]);
+    const float* __restrict__ all = reinterpret_cast<const float*>(P.heap[P.rank] + P.L.pts_all);
+    float* __restrict__ kb = reinterpret_cast<float*>(P.heap[P.rank] + P.L.keybuf);
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < local_n; i += gridDim.x * blockDim.x)
+        kb[i] = all[(size_t)idx[i] * P.dim + axis];
+}
+
+// the key column of the current level: a carried coordinate column, or the gathered keys
+__device__ __forceinline__ const float* key_column(const DistParams& P, int cur, int axis) {
+    return P.ncol ? reinterpret_cast<const float*>(P.heap[P.rank] + P.L.col[cur][axis])
+                  : reinterpret_cast<const float*>(P.heap[P.rank] + P.L.keybuf);
+}
+
 __global__ void k_dist_state_init(DistParams P, LevelGeo g) {
     if (threadIdx.x || blockIdx.x) return;
     DistCtl* c = DCTL(P, P.rank);
@@ -271,7 +313,7 @@ __global__ void __launch_bounds__(512) k_dsample(DistParams P, LevelGeo g, int c
     const Cols src = cols_of(P, P.rank, cur);
     for (unsigned k = tid; k < (unsigned)kDSample; k += 512) {
         const unsigned pos = (unsigned)(((unsigned long long)k * free_n) / kDSample);
-        sm[k] = composite(ordered_key(src.c[axis][pos]), (unsigned)src.idx[pos]);
+        sm[k] = composite(ordered_key(key_column(P, cur, axis)[pos]), (unsigned)src.idx[pos]);
     }
     __syncthreads();
     for (unsigned k = 2; k <= (unsigned)kDSample; k <<= 1)
@@ -349,7 +391,7 @@ __global__ void __launch_bounds__(BLOCK) k_dbracket(DistParams P, LevelGeo g, in
     const unsigned local_n = ctl->cnt;
     const unsigned free_n = (g.j == g.G - 1) ? local_n - 1u : local_n;
     const Cols src = cols_of(P, P.rank, cur);
-    const float* __restrict__ keys = src.c[axis];
+    const float* __restrict__ keys = key_column(P, cur, axis);
     const int32_t* __restrict__ idx = src.idx;
     float* __restrict__ cand_key = reinterpret_cast<float*>(P.heap[P.rank] + P.L.ckey);
     int32_t* __restrict__ cand_idx = reinterpret_cast<int32_t*>(P.heap[P.rank] + P.L.cidx);
@@ -469,7 +511,7 @@ __global__ void __launch_bounds__(BLOCK) k_hist_dist(DistParams P, LevelGeo g, i
     const unsigned free_n = (g.j == g.G - 1) ? local_n - 1u : local_n;  // the range's pinned last element sits on the last member
     const Cols src = cols_of(P, P.rank, cur);
     const bool via = ctl->use_cand != 0;   // after a successful bracket: the compacted candidates of this CTA's chunk
-    const float* __restrict__ keys = via ? reinterpret_cast<const float*>(P.heap[P.rank] + P.L.ckey) : src.c[axis];
+    const float* __restrict__ keys = via ? reinterpret_cast<const float*>(P.heap[P.rank] + P.L.ckey) : key_column(P, cur, axis);
     const int32_t* __restrict__ cand_idx = reinterpret_cast<const int32_t*>(P.heap[P.rank] + P.L.cidx);
     const int32_t* __restrict__ idx = src.idx;
     // the keys are cut into `nchunk` chunks (the geometry k_dbracket compacted the candidates with); a CTA walks
@@ -707,7 +749,9 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
     unsigned bestpos = 0, bestvalid = 0;
     bool has_node = false;
     int node_id = 0;
-    float node_val[NCOL];
+    constexpr int NC1 = NCOL > 0 ? NCOL : 1;   // NCOL == 0 (gather mode): only the index column moves
+    const float* __restrict__ keycol = key_column(P, cur, axis);
+    float node_val[NC1];
 
     if (last_member && blockIdx.x == gridDim.x - 1 && tid == 0) {
         // the range's pinned element: last element of the right child range, i.e. of the group's last member
@@ -722,7 +766,8 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
     for (unsigned tb = b; tb < e; tb += BLOCK * IPT) {
         if (tid < 2) s_cnt[tid] = 0;
         __syncthreads();
-        float val[IPT][NCOL];
+        float val[IPT][NC1];
+        float kf0[IPT];
         int id[IPT];
         unsigned rk[IPT], key[IPT];
         signed char side[IPT];
@@ -733,11 +778,12 @@ __global__ void __launch_bounds__(BLOCK) k_partition_dist(DistParams P, LevelGeo
             id[k] = valid ? src.idx[i] : 0;
 #pragma unroll
             for (int c = 0; c < NCOL; ++c) val[k][c] = valid ? src.c[c][i] : 0.f;
+            kf0[k] = (NCOL == 0 && valid) ? keycol[i] : 0.f;
         }
 #pragma unroll
         for (int k = 0; k < IPT; ++k) {
             unsigned i = tb + k * BLOCK + tid;
-            float kf = val[k][0];
+            float kf = NCOL > 0 ? val[k][0] : kf0[k];
 #pragma unroll
             for (int c = 1; c < NCOL; ++c) kf = (c == axis) ? val[k][c] : kf;
             key[k] = ordered_key(kf);
@@ -969,7 +1015,7 @@ static LevelGeo make_geo(const DistParams& P, int level) {
 
 enum Phase { PH_STATE = 0, PH_HIST, PH_SCAN, PH_CNT_POST, PH_CNT_WAIT, PH_PART, PH_PART_POST, PH_PART_WAIT, PH_MAX_POST,
              PH_MAX_WAIT, PH_FIX_POST, PH_FIX_WAIT, PH_SAMPLE_POST, PH_PIVOT_WAIT, PH_BRACKET_POST, PH_BRACKET_WAIT,
-             kNumPhases };
+             PH_ROWS_PUSH, PH_ROWS_POST, PH_ROWS_WAIT, PH_KEYS, kNumPhases };
 
 // One distributed level in launch order: (phase, pass) pairs.  Drivers of virtual ranks launch every entry for all
 // ranks before the next entry (posts before waits); kd_dist_run walks the same list for its own rank.
@@ -977,6 +1023,10 @@ struct Step { int phase, pass; };
 static int level_schedule(Step* out) {
     int n = 0;
     out[n++] = {PH_STATE, 0};
+    out[n++] = {PH_ROWS_PUSH, 4};   // gather mode, level 0 only: every rank's rows to every rank (no-ops otherwise)
+    out[n++] = {PH_ROWS_POST, 4};
+    out[n++] = {PH_ROWS_WAIT, 4};
+    out[n++] = {PH_KEYS, 4};        // gather mode: the level's split-axis keys
     out[n++] = {PH_SAMPLE_POST, 6};
     out[n++] = {PH_PIVOT_WAIT, 6};
     out[n++] = {PH_BRACKET_POST, 5};
@@ -989,6 +1039,47 @@ static int level_schedule(Step* out) {
 static int dist_grid(unsigned local_n, int min_chunk) {
     int64_t cap = std::max<int64_t>(1, ((int64_t)local_n + min_chunk - 1) / min_chunk);
     return (int)std::min<int64_t>(kTargetCtas, cap);
+}
+
+// K7, bulk part: a finished slice of this rank's tree arrays -> every other GPU's tree arrays.  With an NVLS
+// multicast mapping ONE 16-byte store per chunk is fanned out by the switch (multimem.st lowers to a plain STG on
+// the multicast address); otherwise one store per peer.  Runs on a side stream while the next slice is built.
+struct RepDst { int32_t* perm[kMaxWorld]; float* tp[kMaxWorld]; int n; };
+
+__device__ __forceinline__ void rep_copy(const unsigned* __restrict__ src, unsigned* const* dst, int nd, size_t words,
+                                         size_t tid, size_t nth) {
+    // words [0, words) of src -> the same offsets of every dst; src and dst share their alignment phase
+    const size_t head = min(words, (size_t)((4u - ((reinterpret_cast<uintptr_t>(src) >> 2) & 3u)) & 3u));
+    const size_t body = (words - head) >> 2;
+    for (size_t i = tid; i < head; i += nth)
+        for (int d = 0; d < nd; ++d) dst[d][i] = src[i];
+    const uint4* __restrict__ s4 = reinterpret_cast<const uint4*>(src + head);
+    for (size_t i = tid; i < body; i += nth) {
+        const uint4 v = __ldcs(&s4[i]);
+        for (int d = 0; d < nd; ++d) reinterpret_cast<uint4*>(dst[d] + head)[i] = v;
+    }
+    for (size_t i = head + (body << 2) + tid; i < words; i += nth)
+        for (int d = 0; d < nd; ++d) dst[d][i] = src[i];
+}
+
+__global__ void __launch_bounds__(512) k_replicate(const int32_t* __restrict__ perm, const float* __restrict__ tp,
+                                                   RepDst dst, size_t first, size_t count, int dim) {
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
+    unsigned* d[kMaxWorld];
+    for (int r = 0; r < dst.n; ++r) d[r] = reinterpret_cast<unsigned*>(dst.perm[r] + first);
+    rep_copy(reinterpret_cast<const unsigned*>(perm + first), d, dst.n, count, tid, nth);
+    if (tp) {
+        for (int r = 0; r < dst.n; ++r) d[r] = reinterpret_cast<unsigned*>(dst.tp[r] + first * dim);
+        rep_copy(reinterpret_cast<const unsigned*>(tp + first * dim), d, dst.n, count * dim, tid, nth);
+    }
+}
+
+// gather mode: a run of floats of this rank's point array -> the same offsets of the other ranks' copies
+__global__ void __launch_bounds__(512) k_rows_push(const float* __restrict__ all, RepDst dst, size_t first, size_t count) {
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
+    unsigned* d[kMaxWorld];
+    for (int r = 0; r < dst.n; ++r) d[r] = reinterpret_cast<unsigned*>(dst.tp[r] + first);
+    rep_copy(reinterpret_cast<const unsigned*>(all + first), d, dst.n, count, tid, nth);
 }
 
 // CTA width of k_partition_dist (KD_DIST_PART_BLOCK = 128 | 512).  128-thread CTAs with 512-point tiles: many
@@ -1011,7 +1102,7 @@ static int dist_func_attributes_once() {
     if (dev >= 0 && dev < 64 && done[dev]) return 0;
     e = cudaFuncSetAttribute(k_dpivots, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxWorld * kDSample * 8);
 #define KD_PD_ATTR(NC) if (e == cudaSuccess) e = cudaFuncSetAttribute(k_partition_dist<NC, 512, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, ((NC) + 1) * 2048 * 4)
-    KD_PD_ATTR(1); KD_PD_ATTR(2); KD_PD_ATTR(3); KD_PD_ATTR(4); KD_PD_ATTR(5); KD_PD_ATTR(6); KD_PD_ATTR(7); KD_PD_ATTR(8);
+    KD_PD_ATTR(0); KD_PD_ATTR(1); KD_PD_ATTR(2); KD_PD_ATTR(3); KD_PD_ATTR(4); KD_PD_ATTR(5); KD_PD_ATTR(6); KD_PD_ATTR(7); KD_PD_ATTR(8);
 #undef KD_PD_ATTR
     if (e != cudaSuccess) return fail(std::string("kd_dist: cudaFuncSetAttribute: ") + cudaGetErrorString(e));
     if (dev >= 0 && dev < 64) done[dev] = true;
@@ -1039,6 +1130,35 @@ static int run_phase(const HostCtx& H, int level, int phase, int pass, unsigned 
             }
             k_dist_state_init<<<1, 32, 0, st>>>(P, g);
             KD_DLAUNCH("k_dist_state_init");
+            break;
+        case PH_ROWS_PUSH: {
+            if (P.ncol != 0 || level != 0 || P.world == 1) break;
+            // my slice of the point array (already in my own copy) -> the same rows of every other rank's copy
+            unsigned first = (unsigned)((P.N / P.world) * P.rank);
+            unsigned count = P.N / P.world + (P.rank == P.world - 1 ? P.N % P.world : 0u);   // kdtree_mpi.cpp:208-216
+            RepDst rep{};
+            if (P.mc) { rep.n = 1; rep.tp[0] = (float*)(P.mc + P.L.pts_all); }
+            else for (int r = 0; r < P.world; ++r)
+                if (r != P.rank) rep.tp[rep.n++] = (float*)(P.heap[r] + P.L.pts_all);
+            k_rows_push<<<148, 512, 0, st>>>((const float*)(P.heap[P.rank] + P.L.pts_all), rep, (size_t)first * P.dim,
+                                             (size_t)count * P.dim);
+            KD_DLAUNCH("k_rows_push");
+            break;
+        }
+        case PH_ROWS_POST:
+            if (P.ncol != 0 || level != 0 || P.world == 1) break;
+            k_flag_post<<<1, 32, 0, st>>>(P, g, F_ROWS, epoch);
+            KD_DLAUNCH("k_flag_post");
+            break;
+        case PH_ROWS_WAIT:
+            if (P.ncol != 0 || level != 0 || P.world == 1) break;
+            k_flag_wait<<<1, 32, 0, st>>>(P, g, F_ROWS, epoch);
+            KD_DLAUNCH("k_flag_wait");
+            break;
+        case PH_KEYS:
+            if (P.ncol != 0) break;
+            k_dist_gather_keys<<<dist_grid(local_cap, 2048), 256, 0, st>>>(P, g, cur, axis);
+            KD_DLAUNCH("k_dist_gather_keys");
             break;
         case PH_SAMPLE_POST:
             k_dsample<<<1, 512, 0, st>>>(P, g, cur, axis, epoch);
@@ -1086,6 +1206,7 @@ static int run_phase(const HostCtx& H, int level, int phase, int pass, unsigned 
             k_partition_dist<NC, 512, 4><<<grid, 512, (size_t)((NC) + 1) * 2048 * 4, st>>>(P, g, cur, axis, H.with_tp); \
     } while (0)
             switch (P.ncol) {
+                case 0: KD_PD(0); break;
                 case 1: KD_PD(1); break;
                 case 2: KD_PD(2); break;
                 case 3: KD_PD(3); break;
@@ -1132,39 +1253,6 @@ static int dist_levels(int world) {
     int l = 0;
     while ((1 << l) < world) ++l;
     return l;
-}
-
-// K7, bulk part: a finished slice of this rank's tree arrays -> every other GPU's tree arrays.  With an NVLS
-// multicast mapping ONE 16-byte store per chunk is fanned out by the switch (multimem.st lowers to a plain STG on
-// the multicast address); otherwise one store per peer.  Runs on a side stream while the next slice is built.
-struct RepDst { int32_t* perm[kMaxWorld]; float* tp[kMaxWorld]; int n; };
-
-__device__ __forceinline__ void rep_copy(const unsigned* __restrict__ src, unsigned* const* dst, int nd, size_t words,
-                                         size_t tid, size_t nth) {
-    // words [0, words) of src -> the same offsets of every dst; src and dst share their alignment phase
-    const size_t head = min(words, (size_t)((4u - ((reinterpret_cast<uintptr_t>(src) >> 2) & 3u)) & 3u));
-    const size_t body = (words - head) >> 2;
-    for (size_t i = tid; i < head; i += nth)
-        for (int d = 0; d < nd; ++d) dst[d][i] = src[i];
-    const uint4* __restrict__ s4 = reinterpret_cast<const uint4*>(src + head);
-    for (size_t i = tid; i < body; i += nth) {
-        const uint4 v = __ldcs(&s4[i]);
-        for (int d = 0; d < nd; ++d) reinterpret_cast<uint4*>(dst[d] + head)[i] = v;
-    }
-    for (size_t i = head + (body << 2) + tid; i < words; i += nth)
-        for (int d = 0; d < nd; ++d) dst[d][i] = src[i];
-}
-
-__global__ void __launch_bounds__(512) k_replicate(const int32_t* __restrict__ perm, const float* __restrict__ tp,
-                                                   RepDst dst, size_t first, size_t count, int dim) {
-    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
-    unsigned* d[kMaxWorld];
-    for (int r = 0; r < dst.n; ++r) d[r] = reinterpret_cast<unsigned*>(dst.perm[r] + first);
-    rep_copy(reinterpret_cast<const unsigned*>(perm + first), d, dst.n, count, tid, nth);
-    if (tp) {
-        for (int r = 0; r < dst.n; ++r) d[r] = reinterpret_cast<unsigned*>(dst.tp[r] + first * dim);
-        rep_copy(reinterpret_cast<const unsigned*>(tp + first * dim), d, dst.n, count * dim, tid, nth);
-    }
 }
 
 // streams + events of the sliced local phase, one set per device: slice c is built and replicated on stream c,
@@ -1221,7 +1309,8 @@ static int local_build(const HostCtx& H, cudaStream_t st) {
         buf[b].idx = (int32_t*)(base + P.L.idx[b]);
     }
     BuildScratch sc;
-    sc.keybuf = nullptr;
+    const float* all_pts = P.ncol ? nullptr : (const float*)(base + P.L.pts_all);   // gather mode: keys come from here
+    sc.keybuf = P.ncol ? nullptr : (float*)(base + P.L.keybuf);
     sc.st = (SegState*)(base + P.L.st);
     sc.ghist = (unsigned*)(base + P.L.ghist);
     sc.rec = (MaxRec*)(base + P.L.lrec);
@@ -1250,8 +1339,11 @@ static int local_build(const HostCtx& H, cudaStream_t st) {
         }
     }
     const int kChunkLevel = chunk_level();
-    if (P.world == 1 || n < kChunkMinLocal || kChunkLevel == 0)
-        return build_core(buf, L & 1, (int64_t)n, P.dim, P.ncol, L, lo, out, nullptr, sc, st, -1, nullptr);
+    if (P.world == 1 || n < kChunkMinLocal || kChunkLevel == 0 || P.ncol == 0) {
+        if (P.ncol == 0)   // tree_points are gathered from the full point array once the permutation is complete
+            for (int r = 0; r < out.n; ++r) out.tp[r] = nullptr;
+        return build_core(buf, L & 1, (int64_t)n, P.dim, P.ncol, L, lo, out, all_pts, sc, st, -1, nullptr);
+    }
 
     // Overlap of the sub-tree all-gather with the local phase: the top kChunkLevel local levels run on the whole
     // slice (their few nodes go to every replica directly); then the slice is finished range by range into this
@@ -1331,13 +1423,13 @@ static int fill_ctx(const kd_dist_ctx* c, kd::HostCtx& H) {
     if (!c) return kd::fail("kd_dist: null context");
     if (c->world < 1 || c->world > kd::kMaxWorld || (c->world & (c->world - 1))) return kd::fail("kd_dist: world must be 1, 2, 4 or 8");
     if (c->rank < 0 || c->rank >= c->world) return kd::fail("kd_dist: bad rank");
-    if (c->dim < 1 || c->dim > kd::kMaxCarry) return kd::fail("kd_dist: the distributed build supports dim <= 8");
+    if (c->dim < 1 || c->dim > 4096) return kd::fail("kd_dist: dim must be in [1, 4096]");
     if (c->n_total < 64ll * c->world || c->n_total >= (1ll << 31))
         return kd::fail("kd_dist: need 64 * world <= n_total < 2^31");
     H.P.world = c->world;
     H.P.rank = c->rank;
     H.P.dim = c->dim;
-    H.P.ncol = c->dim;
+    H.P.ncol = c->dim <= kd::kMaxCarry ? c->dim : 0;   // larger dim: gather mode
     H.P.N = (unsigned)c->n_total;
     H.with_tp = c->with_tree_points != 0;
     H.P.L = kd::make_layout(c->n_total, c->dim, c->world, H.with_tp);
@@ -1349,12 +1441,12 @@ static int fill_ctx(const kd_dist_ctx* c, kd::HostCtx& H) {
 }
 
 size_t kd_dist_heap_bytes(int64_t n_total, int dim, int world, int with_tree_points) {
-    if (n_total <= 0 || dim <= 0 || dim > kd::kMaxCarry || world < 1 || world > kd::kMaxWorld) return 0;
+    if (n_total <= 0 || dim <= 0 || dim > 4096 || world < 1 || world > kd::kMaxWorld) return 0;
     return kd::make_layout(n_total, dim, world, with_tree_points != 0).bytes;
 }
 
 int kd_dist_offsets(int64_t n_total, int dim, int world, int with_tree_points, size_t* perm_off, size_t* tp_off) {
-    if (n_total <= 0 || dim <= 0 || dim > kd::kMaxCarry || world < 1 || world > kd::kMaxWorld)
+    if (n_total <= 0 || dim <= 0 || dim > 4096 || world < 1 || world > kd::kMaxWorld)
         return kd::fail("kd_dist_offsets: bad arguments");
     kd::DistLayout L = kd::make_layout(n_total, dim, world, with_tree_points != 0);
     if (perm_off) *perm_off = L.perm;
@@ -1369,8 +1461,11 @@ int kd_dist_init(const kd_dist_ctx* ctx, const float* local_points, int64_t loca
     cudaStream_t st = (cudaStream_t)stream;
     // control words and flags start at zero once per heap; epochs only grow afterwards
     kd::reset_launches();
-    kd::k_dist_init<<<(unsigned)((local_n + kd::kDInitRows - 1) / kd::kDInitRows), kd::kDInitBlock, 0, st>>>(
-        H.P, local_points, (unsigned)local_n, (unsigned)first_row);
+    if (H.P.ncol)
+        kd::k_dist_init<<<(unsigned)((local_n + kd::kDInitRows - 1) / kd::kDInitRows), kd::kDInitBlock, 0, st>>>(
+            H.P, local_points, (unsigned)local_n, (unsigned)first_row);
+    else
+        kd::k_dist_init_rows<<<148 * 4, 256, 0, st>>>(H.P, local_points, (unsigned)local_n, (unsigned)first_row);
     kd::count_launch();
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : kd::fail(std::string("kd_dist_init: ") + cudaGetErrorString(e));
@@ -1401,6 +1496,17 @@ int kd_dist_done(const kd_dist_ctx* ctx, int post, uint64_t serial, void* stream
     return e == cudaSuccess ? 0 : kd::fail(std::string("kd_dist_done: ") + cudaGetErrorString(e));
 }
 
+/* after the done-barrier: in gather mode (dim > 8) every rank fills its tree_points from its own copy of the point
+ * array and the complete permutation (nothing to do otherwise) */
+int kd_dist_finish(const kd_dist_ctx* ctx, void* stream) {
+    kd::HostCtx H;
+    if (int rc = fill_ctx(ctx, H)) return rc;
+    if (H.P.ncol != 0 || !H.with_tp) return 0;
+    unsigned char* base = H.P.heap[H.P.rank];
+    return kd_gather_rows_gpu((const float*)(base + H.P.L.pts_all), (const int32_t*)(base + H.P.L.perm), (int64_t)H.P.N,
+                              H.P.dim, (float*)(base + H.P.L.tp), stream);
+}
+
 // one rank's whole build, in program order (one process per GPU)
 int kd_dist_run(const kd_dist_ctx* ctx, uint64_t serial, void* stream) {
     kd::HostCtx H;
@@ -1414,7 +1520,8 @@ int kd_dist_run(const kd_dist_ctx* ctx, uint64_t serial, void* stream) {
             if (int rc = kd::run_phase(H, level, steps[k].phase, steps[k].pass, serial, st)) return rc;
     if (int rc = kd::local_build(H, st)) return rc;
     if (int rc = kd_dist_done(ctx, 1, serial, stream)) return rc;
-    return kd_dist_done(ctx, 0, serial, stream);
+    if (int rc = kd_dist_done(ctx, 0, serial, stream)) return rc;
+    return kd_dist_finish(ctx, stream);
 }
 
 /* Synchronises the stream and copies this rank's counters of the level that ran last to the host:

@@ -54,8 +54,6 @@ class _Base:
     def __init__(self, n_total: int, dim: int, world: int, with_tree_points: bool):
         if world & (world - 1) or not 1 <= world <= 8:
             raise ValueError("world must be 1, 2, 4 or 8")
-        if dim > 8:
-            raise ValueError("the distributed build carries coordinates with the points and supports dim <= 8")
         self.n_total, self.dim, self.world, self.with_tp = int(n_total), int(dim), int(world), bool(with_tree_points)
         self.heap_bytes = int(lib().kd_dist_heap_bytes(self.n_total, self.dim, self.world, int(self.with_tp)))
         if self.heap_bytes == 0:
@@ -117,6 +115,8 @@ class EmulatedDistBuild(_Base):
             for post in (1, 0):
                 for ctx in self.ctxs:
                     check(L.kd_dist_done(C.byref(ctx), post, self.serial, st), "kd_dist_done")
+            for ctx in self.ctxs:
+                check(L.kd_dist_finish(C.byref(ctx), st), "kd_dist_finish")
             for ctx in self.ctxs:
                 check(L.kd_dist_status(C.byref(ctx), st), "kd_dist_status")
         return [self._views(h) for h in self.heaps]

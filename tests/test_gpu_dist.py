@@ -88,6 +88,22 @@ def test_emulated_ranks_large_local_phase(kd):
             assert torch.equal(outs[-1][1].cpu(), pts[ref.cpu().long()])
 
 
+@pytest.mark.parametrize("n,dim,world", [(20000, 16, 2), (50001, 128, 4), (30000, 33, 8)])
+def test_emulated_ranks_high_dimension_gather_mode(kd, n, dim, world):
+    # dim > 8 (the reference's default problem is 128-D, Utility.cpp:98): every rank receives all points once, only
+    # indices move through the distributed levels, keys are gathered per level
+    from parallel_kd_tree_b200.parallel.dist_build import EmulatedDistBuild
+    pts = kd.ops.generate_uniform(11, dim, n)
+    ref = kd.ops.build(pts)[0]
+    eb = EmulatedDistBuild(n, dim, world)
+    for trial in range(2):
+        outs = eb.build(pts)
+        torch.cuda.synchronize()
+        for r, (perm, tp) in enumerate(outs):
+            assert torch.equal(perm.cpu(), ref), f"rank {r} trial {trial}"
+        assert torch.equal(outs[0][1].cpu(), pts[ref.long()]) and torch.equal(outs[-1][1].cpu(), pts[ref.long()])
+
+
 def test_library_sort_baseline_on_gpu_matches(kd):
     from parallel_kd_tree_b200.parallel.nccl_baseline import sort_build
     pts = kd.ops.generate_uniform(2, 3, 200000)

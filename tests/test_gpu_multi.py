@@ -32,7 +32,7 @@ def _torchrun(world, args, env=None, port=29600, timeout=600):
 @pytest.mark.parametrize("backend", ["symm", "ipc"])
 @pytest.mark.parametrize("world", WORLDS)
 def test_multi_process_global_build_equals_single_gpu_build(world, backend):
-    specs = ["100003x3", "1048576x2", "300000x8", "clustered:2097152x3"]
+    specs = ["100003x3", "1048576x2", "300000x8", "clustered:2097152x3", "60000x128"]
     r = _torchrun(world, ["tools/dist_check.py"] + specs, env={"KD_DIST_BACKEND": backend},
                   port=29600 + world + (10 if backend == "ipc" else 0))
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]

@@ -153,6 +153,7 @@ for level in range(levels):
 kd._lib.check(L.kd_dist_local_build(C.byref(b.ctx), st), "local")
 kd._lib.check(L.kd_dist_done(C.byref(b.ctx), 1, b.serial, st), "done")
 kd._lib.check(L.kd_dist_done(C.byref(b.ctx), 0, b.serial, st), "done")
+kd._lib.check(L.kd_dist_finish(C.byref(b.ctx), st), "finish")
 torch.cuda.synchronize()
 b.status()
 if rank == 0:
