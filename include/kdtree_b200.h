@@ -171,6 +171,14 @@ size_t kd_forest_buf_bytes(int nq);
 int kd_forest_min_reduce(void* root_buf, void* my_buf, int rank, int world, const float* dist, int nq, float* out,
                          uint64_t epoch, int* err, void* stream);
 
+/* ---- bounding box over ranks (K12): per-axis min / max of a point set spread over W GPUs, all-reduced with system-scope
+ * atomicMin / atomicMax into every rank's small symmetric buffer over peer memory (no collective library call).
+ * bufs[r] = rank r's buffer (kd_peer_minmax_buf_bytes(dim) bytes from kd_symm_alloc) as addressable from this rank;
+ * `epoch` must grow with every call.  No counterpart in the reference. ---- */
+size_t kd_peer_minmax_buf_bytes(int dim);
+int kd_peer_minmax_reduce(void* const* bufs, int rank, int world, const float* local_min, const float* local_max, int dim,
+                          float* out_min, float* out_max, uint64_t epoch, int* err, void* stream);
+
 /* ---- symmetric-heap runtime: allocation and CUDA IPC mapping (handle exchange is the caller's job) ---- */
 int kd_symm_alloc(size_t bytes, void** ptr, void* handle64);
 int kd_symm_open(const void* handle64, void** ptr);

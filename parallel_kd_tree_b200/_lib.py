@@ -79,6 +79,8 @@ def _declare(lib):
         "kd_dist_status": (i32, [C.POINTER(DistCtx), vp]),
         "kd_forest_buf_bytes": (C.c_size_t, [i32]),
         "kd_forest_min_reduce": (i32, [vp, vp, i32, i32, vp, i32, vp, C.c_uint64, vp, vp]),
+        "kd_peer_minmax_buf_bytes": (C.c_size_t, [i32]),
+        "kd_peer_minmax_reduce": (i32, [C.POINTER(vp), i32, i32, vp, vp, i32, vp, vp, C.c_uint64, vp, vp]),
         "kd_symm_alloc": (i32, [C.c_size_t, C.POINTER(vp), vp]),
         "kd_symm_open": (i32, [vp, C.POINTER(vp)]),
         "kd_symm_close": (i32, [vp]),

@@ -1685,3 +1685,73 @@ int kd_forest_min_reduce(void* root_buf, void* my_buf, int rank, int world, cons
     return e == cudaSuccess ? 0 : kd::fail(std::string("kd_forest_min_reduce: ") + cudaGetErrorString(e));
 }
 }
+
+// ------------------------------------------------------------------------------------------------
+// K12 over ranks: per-axis min / max of a point set spread over W GPUs, as ONE kernel per rank over peer memory
+// (an all-reduce: every rank ends up with the result).  Every rank initialises its own accumulator and tells every
+// peer so; folds its local bounds into EVERY rank's accumulator with system-scope atomicMin / atomicMax on the
+// order-preserving keys; signals every peer; waits for all signals and decodes.  No collective library call.
+// Buffer per rank (a small symmetric allocation): u64 ready[8] | u64 done[8] | u32 mn[dim] | u32 mx[dim].
+// ------------------------------------------------------------------------------------------------
+namespace kd {
+struct MinMaxBuf {
+    unsigned long long ready[kMaxWorld];
+    unsigned long long done[kMaxWorld];
+    unsigned v[1];   // mn[dim], mx[dim]
+};
+struct MinMaxPeers { MinMaxBuf* b[kMaxWorld]; };
+
+__global__ void __launch_bounds__(256) k_peer_minmax(MinMaxPeers peers, int rank, int world, const float* __restrict__ lmin,
+                                                     const float* __restrict__ lmax, int dim, float* __restrict__ out_min,
+                                                     float* __restrict__ out_max, unsigned long long epoch, int* err) {
+    __shared__ int s_ok;
+    const int tid = threadIdx.x;
+    MinMaxBuf* mine = peers.b[rank];
+    if (tid == 0) s_ok = 1;
+    for (int d = tid; d < dim; d += blockDim.x) { mine->v[d] = 0xffffffffu; mine->v[dim + d] = 0u; }
+    __threadfence_system();
+    __syncthreads();
+    if (tid < world) st_release_sys(&peers.b[tid]->ready[rank], epoch);          // "my accumulator is ready", to everyone
+    if (tid < world && !wait_flag(&mine->ready[tid], epoch)) { atomicExch(err, 700); s_ok = 0; }
+    __syncthreads();
+    if (!s_ok) return;   // some accumulator may not be initialised: fold nothing, signal nothing
+    for (int r = 0; r < world; ++r)
+        for (int d = tid; d < dim; d += blockDim.x) {
+            atomicMin_system(&peers.b[r]->v[d], ordered_key(lmin[d]));
+            atomicMax_system(&peers.b[r]->v[dim + d], ordered_key(lmax[d]));
+        }
+    __threadfence_system();
+    __syncthreads();
+    if (tid < world) st_release_sys(&peers.b[tid]->done[rank], epoch);
+    if (tid < world && !wait_flag(&mine->done[tid], epoch)) { atomicExch(err, 701); s_ok = 0; }
+    __syncthreads();
+    if (!s_ok) return;
+    auto back = [](unsigned k) { return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k); };
+    for (int d = tid; d < dim; d += blockDim.x) {
+        out_min[d] = back(__ldcg(&mine->v[d]));
+        out_max[d] = back(__ldcg(&mine->v[dim + d]));
+    }
+}
+}  // namespace kd
+
+extern "C" {
+size_t kd_peer_minmax_buf_bytes(int dim) { return sizeof(kd::MinMaxBuf) + (size_t)2 * (dim > 0 ? dim : 1) * 4 + 64; }
+
+/* bufs[r]: rank r's buffer (kd_peer_minmax_buf_bytes, from kd_symm_alloc, zeroed) as addressable from this rank;
+ * local_min / local_max: this rank's per-axis bounds (device, e.g. from kd_bbox_gpu); out_*: the bounds over all ranks
+ * (device); epoch must grow with every call; err: device int. */
+int kd_peer_minmax_reduce(void* const* bufs, int rank, int world, const float* local_min, const float* local_max, int dim,
+                          float* out_min, float* out_max, uint64_t epoch, int* err, void* stream) {
+    if (!bufs || !local_min || !local_max || !out_min || !out_max || !err || dim <= 0 || world < 1 ||
+        world > kd::kMaxWorld || rank < 0 || rank >= world)
+        return kd::fail("kd_peer_minmax_reduce: bad arguments");
+    kd::MinMaxPeers P{};
+    for (int r = 0; r < world; ++r) {
+        if (!bufs[r]) return kd::fail("kd_peer_minmax_reduce: missing buffer pointer");
+        P.b[r] = (kd::MinMaxBuf*)bufs[r];
+    }
+    kd::k_peer_minmax<<<1, 256, 0, (cudaStream_t)stream>>>(P, rank, world, local_min, local_max, dim, out_min, out_max, epoch, err);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : kd::fail(std::string("kd_peer_minmax_reduce: ") + cudaGetErrorString(e));
+}
+}

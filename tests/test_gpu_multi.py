@@ -50,3 +50,12 @@ def test_forest_mode_prints_the_reference_mpi_lines(world, oracle):
     lines = [ln for ln in r.stdout.splitlines() if ln.startswith("ID:")]
     assert "\n".join(lines) + "\n" == want
     assert "READY" in r.stdout and r.stdout.rstrip().endswith("DONE")
+
+
+@needs2
+@pytest.mark.parametrize("world", WORLDS[:1] + WORLDS[-1:] if len(WORLDS) > 1 else WORLDS)
+def test_peer_memory_bounding_box_all_reduce(world):
+    # K12 over ranks: system-scope atomicMin / atomicMax into every rank's symmetric buffer, no collective call
+    r = _torchrun(world, ["tools/bbox_check.py"], port=29680 + world)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    assert "MISMATCH" not in r.stdout and r.stdout.count(": OK") == 9 * world
