@@ -31,7 +31,14 @@ bench-multi:
 sass:
 	$(PY) tools/dump_sass.py
 
+debug:            ## the -DKD_DEBUG variant (bounds assertions on every computed store offset) + its test
+	$(PY) -m parallel_kd_tree_b200.build --debug
+	$(PY) -m pytest tests/test_gpu_debug_build.py -x -q -m gpu
+
+docs:
+	$(PY) tools/gen_api_docs.py
+
 clean:
 	rm -rf parallel_kd_tree_b200/_C baseline/_ref gpurun_out .pytest_cache
 
-.PHONY: all build reference sequential run_sequential mpi run_mpi test test-gpu bench bench-multi sass clean
+.PHONY: all build reference sequential run_sequential mpi run_mpi test test-gpu bench bench-multi sass debug docs clean

@@ -4,24 +4,30 @@
 // builds over all N points (kdtree_sequential.cpp:30-66), bit for bit.
 //
 // The top log2(W) levels span GPUs.  At level l the W ranks form W >> l groups; group g owns range g of
-// that level, spread over its members in member order.  Per level:
-//   K5  k_hist_dist + k_scan_dist   radix select fused with a one-shot P2P reduction: the last CTA of a
-//                                   rank's histogram kernel stores the rank's 2048 bins into a slot in
-//                                   EVERY member's memory and raises a flag there; every member sums the
-//                                   slots and picks the same bin.  No collective call, no host round trip.
-//   K6  k_partition_dist            stream-compaction partition whose stores go straight into the owner
-//                                   GPU's next-level buffers (P2P stores); the node goes to every GPU's
-//                                   tree arrays; per-rank counts are exchanged the same one-shot way.
+// that level, spread over its members.  Per level (level_schedule() lists the steps):
+//   K5  k_dsample / k_dpivots /     sample bracket across the group: sorted samples to every member (one-shot P2P),
+//       k_dbracket(_wait)           identical pivots everywhere, ONE counting / compaction pass over the local keys;
+//       k_hist_dist + k_scan_dist   radix select over the ~5 % candidates; the last CTA of a rank's histogram kernel
+//                                   publishes its 2048 bins with NVLS multimem.red into the group's accumulator on
+//                                   every GPU (or stores them into a slot in every member's memory where no
+//                                   multicast mapping exists) and bumps an arrival counter / flag; every member
+//                                   picks the same bin.  No collective call, no host round trip.
+//   K6  k_partition_dist            stream-compaction partition whose stores go straight into the owner GPUs'
+//                                   next-level buffers (staged runs, 16-byte P2P stores); members' runs are ordered so
+//                                   that every GPU keeps one of its halves at home; the node goes to every GPU's
+//                                   tree arrays; per-rank counts are exchanged one-shot.
 //       k_max_*                     the left range's largest element is swapped into its last slot
 //                                   (it is the next pinned element) by the GPU that owns that slot.
 // After the last distributed level every GPU owns one complete sub-range and finishes it with the
 // single-GPU kernels, whose stores are replicated into every GPU's tree arrays (K7: the sub-tree
-// all-gather is fused into the finisher's write-out).
+// all-gather is fused into k_subtree's write-out; k_replicate serves the optional sliced local phase).
+// dim > 8: gather mode (k_rows_push once, k_dist_gather_keys per level, only indices move).
 //
 // Every wait on a peer is a separate tiny kernel from the matching post, so the same code also runs
 // as W *virtual* ranks of one process on one GPU (posts of all ranks are launched before the waits);
 // that is how the logic is tested without a multi-GPU box.  Flags carry a monotonically increasing
-// epoch and are never reset.  Spins give up after ~2 s and record an error instead of hanging the GPU.
+// epoch and are never reset.  Waits give up after 10 s of wall time, record an error, and every later kernel of the
+// build returns at once (kd_dist_status reports it).  TMA is used for loads of this GPU's own memory only.
 #include <cuda_runtime.h>
 
 #include <algorithm>
