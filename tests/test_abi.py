@@ -29,3 +29,15 @@ def test_torch_ops_are_registered_and_agree_with_the_python_entry_points(kd):
     assert all(torch.equal(x, y) for x, y in zip(a, b))
     assert all(torch.equal(x, y) for x, y in zip(kd.ops.materialize_nodes(perm), torch.ops.kd.materialize_nodes(perm)))
     assert all(torch.equal(x, y) for x, y in zip(kd.ops.bbox(pts), torch.ops.kd.bbox(pts)))
+
+
+def test_distributed_level_schedule_posts_before_waits():
+    # every wait phase of a distributed level has its post phase earlier in the list (virtual-rank drivers rely on it)
+    from parallel_kd_tree_b200.parallel import dist_build as db
+    steps = [ph for ph, _ in db.level_schedule()]
+    pairs = [(db.PH_SAMPLE_POST, db.PH_PIVOT_WAIT), (db.PH_BRACKET_POST, db.PH_BRACKET_WAIT), (db.PH_HIST, db.PH_SCAN),
+             (db.PH_CNT_POST, db.PH_CNT_WAIT), (db.PH_PART_POST, db.PH_PART_WAIT), (db.PH_MAX_POST, db.PH_MAX_WAIT),
+             (db.PH_FIX_POST, db.PH_FIX_WAIT)]
+    for post, wait in pairs:
+        assert post in steps and wait in steps and steps.index(post) < steps.index(wait)
+    assert steps[0] == db.PH_STATE and steps.count(db.PH_HIST) == 6 and steps.count(db.PH_PART) == 1
