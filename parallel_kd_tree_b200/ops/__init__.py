@@ -12,11 +12,11 @@ Reference parity: ``generate_uniform`` = Utility.cpp:6-18 / kdtree_mpi.cpp:19-41
 ``materialize_nodes`` = Node.hpp:35-45.
 """
 from .generate import generate_clustered, generate_uniform, generate_problem
-from .build import build, build_workspace_bytes, build_into, last_launch_count, check_tree, build_cpu_sortref
+from .build import build, build_workspace_bytes, build_into, last_launch_count, check_tree, build_cpu_sortref, GraphedBuild
 from .query import nearest, knn, gather_rows, materialize_nodes, bbox, query_order
 
 __all__ = [
     "generate_uniform", "generate_clustered", "generate_problem",
-    "build", "build_into", "build_workspace_bytes", "last_launch_count", "check_tree", "build_cpu_sortref",
+    "build", "build_into", "build_workspace_bytes", "GraphedBuild", "last_launch_count", "check_tree", "build_cpu_sortref",
     "nearest", "knn", "gather_rows", "materialize_nodes", "bbox", "query_order",
 ]

@@ -84,3 +84,16 @@ def test_large_build_rule_check(kd):
     perm, _ = kd.ops.build(pts.cuda())
     ref = kd.ops.build(pts)[0]
     assert torch.equal(perm.cpu(), ref)
+
+
+def test_graphed_build_replays_give_the_same_trees(kd):
+    # the whole launch sequence captured in a CUDA graph; new points are copied into the object's input tensor
+    n, dim = 300000, 3
+    gb = kd.ops.GraphedBuild(n, dim)
+    for seed in (3, 4, 5):
+        pts = kd.ops.generate_uniform(seed, dim, n)
+        gb.points.copy_(pts)
+        gb.run(verify=True)
+        ref = kd.ops.build(pts)[0]
+        assert torch.equal(gb.perm.cpu(), ref)
+        assert torch.equal(gb.tree_points.cpu(), pts[ref.long()])
